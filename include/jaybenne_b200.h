@@ -238,8 +238,13 @@ jb_status jb_num_particles(jb_ctx *ctx, int64_t *n_local);
 jb_status jb_get_particles(jb_ctx *ctx, const jb_particles *dst, int64_t capacity, int64_t *n);
 /* replaces the local swarm with `n` host particles (Parthenon adapter: swarm -> ctx) */
 jb_status jb_set_particles(jb_ctx *ctx, const jb_particles *src, int64_t n);
-/* cumulative stats since the last jb_radiation_step began */
+/* cumulative stats since the last jb_radiation_step / jb_stats_begin began */
 jb_status jb_get_stats(jb_ctx *ctx, jb_cycle_stats *stats);
+/* zero the counters and record n_start / e_start: for hosts that drive the individual
+ * tasks themselves (jb_radiation_step does this internally) */
+jb_status jb_stats_begin(jb_ctx *ctx);
+/* CUDA kernels launched by this context since jb_create (diagnostics / bench.py) */
+int64_t jb_kernel_launches(const jb_ctx *ctx);
 
 /* ---- event log (parity / debugging) --------------------------------------------------- */
 jb_status jb_event_log_enable(jb_ctx *ctx, int64_t capacity); /* 0 disables */

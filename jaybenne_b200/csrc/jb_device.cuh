@@ -1,0 +1,444 @@
+// jb_device.cuh — device-side building blocks of the B200 IMC/DDMC hot path:
+// per-particle Philox streams, the EOS / opacity / scattering closures, and the
+// per-segment physics (IMC step, DDMC albedo + step, isotropic scatter, Planck sampler,
+// block-face resampling). Everything here is FP64 and is written as explicit IEEE
+// operations (the library is compiled with -fmad=false; fused operations only appear as
+// explicit fma() inside jb_math.h) so that a particle history is bit-identical to the
+// CPU oracle's on the same stream.
+//
+// Reference behaviour followed (lanl/jaybenne @ 04947dfa):
+//   src/jaybenne/transport_utils.hpp:23-39,111-160,163-277,279-397
+//   src/jaybenne/scattering.hpp:21-29, src/jaybenne/planck.hpp:27-50
+//   src/jaybenne/sample_ddmc_bface.cpp:24-78
+//   singularity-opac photons/{gray,epbremsstrahlung,non_cgs}_photons.hpp,
+//   photons/{gray_s,thomson_s,non_cgs_s}_photons.hpp, singularity-eos eos_ideal.hpp:55-58,100-103
+#ifndef JAYBENNE_B200_JB_DEVICE_CUH_
+#define JAYBENNE_B200_JB_DEVICE_CUH_
+
+#include <cuda_runtime.h>
+#include <float.h>
+#include <stdint.h>
+
+#include "../../include/jaybenne_b200.h"
+#include "jb_math.h"
+
+namespace jbd {
+
+// stream selectors folded into the Philox key (particle histories / per-cell rounding)
+static constexpr uint32_t STREAM_PARTICLE = 0u;
+static constexpr uint32_t STREAM_CELL = 0x5EED0001u;
+
+static constexpr double JB_PI = 3.14159265358979323846;
+static constexpr double EPS10 = 10 * DBL_EPSILON;            // parthenon::robust::EPS
+static constexpr double EPS_IMC = 1.0e6 * EPS10;             // transport_utils.hpp:23
+static constexpr double EPS_DDMC = 1.0e8 * EPS10;            // transport_utils.hpp:24
+static constexpr double LAM_EXT = 0.7104;                    // extrapolation distance
+
+// ---------------------------------------------------------------------------------------
+// Philox4x32-10 counter generator. One particle owns the stream
+//   counter = (draw >> 1, birth index, birth gid, source call), key = (seed_lo, seed_hi ^ stream)
+// and double #n is built from words (2*(n&1), 2*(n&1)+1) of block n>>1. The generated
+// block is cached so two consecutive draws cost one Philox evaluation.
+struct Rng {
+  uint32_t id0, id1, id2, n, k0, k1;
+  uint32_t w[4];
+  uint32_t have;  // block index held in w (0xffffffff = none)
+
+  __device__ __forceinline__ void init(uint32_t a, uint32_t b, uint32_t c, uint32_t draws, uint32_t key0,
+                                       uint32_t key1) {
+    id0 = a; id1 = b; id2 = c; n = draws; k0 = key0; k1 = key1;
+    have = 0xffffffffu;
+  }
+  __device__ __forceinline__ void refill(uint32_t blk) {
+    uint32_t c0 = blk, c1 = id0, c2 = id1, c3 = id2, a = k0, b = k1;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+      const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+      const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+      c0 = hi1 ^ c1 ^ a;
+      c1 = lo1;
+      c2 = hi0 ^ c3 ^ b;
+      c3 = lo0;
+      a += 0x9E3779B9u;
+      b += 0xBB67AE85u;
+    }
+    w[0] = c0; w[1] = c1; w[2] = c2; w[3] = c3;
+    have = blk;
+  }
+  __device__ __forceinline__ double drand() {
+    const uint32_t blk = n >> 1;
+    if (blk != have) refill(blk);
+    const bool odd = (n & 1u) != 0;
+    const uint32_t lo = odd ? w[2] : w[0], hi = odd ? w[3] : w[1];
+    const uint64_t u = ((uint64_t)hi << 32) | lo;
+    ++n;
+    return (double)(u >> 11) * 1.1102230246251565e-16;
+  }
+};
+
+// ---------------------------------------------------------------------------------------
+// The three closures jaybenne::Initialize is handed (jaybenne.cpp:227-233), flattened to
+// plain numbers. The host fills this once (jb_lib.cu: make_closure) with the same libm
+// calls the CPU side uses for the derived constants.
+struct Closure {
+  int opacity_model, scattering_model, gray_mode;
+  double kappa, sigma, apm, cv;
+  double time_unit, length_unit, temp_unit, rho_unit, freq_unit, inv_emiss_unit;
+  double c_code, sb_code;
+  double bt_num, bt_den;            // 8 pi^5 kb^4, 15 c^2 h^3
+  double sigma_thomson;
+  double ep_mmw, ep_prefac;
+  double h, kb, c, me;              // CGS constants as singularity-opac derives them
+  double two_h_over_c2;             // unused in parity arithmetic; kept for diagnostics
+  double pi4;                       // pow(pi, 4) (planck.hpp:30)
+};
+
+// IdealGas::TemperatureFromDensityInternalEnergy, eos_ideal.hpp:55-58
+__device__ __forceinline__ double eos_temperature(const Closure &cl, double sie) {
+  const double q = sie / cl.cv;
+  return 0.0 > q ? 0.0 : q;
+}
+
+// PlanckDistribution::ThermalDistributionOfTNu, thermal_distributions_photons.hpp:31-37
+__device__ __forceinline__ double planck_bnu(const Closure &cl, double temp, double nu) {
+  const double x = cl.h * nu / (cl.kb * temp);
+  return (2. * cl.h * nu * nu * nu / (cl.c * cl.c)) * 1. / jbm::expm1(x);
+}
+// singularity robust::ratio, robust_utils.hpp:49-52
+__device__ __forceinline__ double robust_ratio(double a, double b) {
+  const int sgn = (0.0 <= b) - (b < 0.0);
+  return a / (b + sgn * (10 * DBL_MIN));
+}
+// EPBremss::EmissivityPerNuOmega, epbremsstrahlung_opacity_photons.hpp:88-96
+__device__ __forceinline__ double epbremss_jnu(const Closure &cl, double rho, double temp, double nu) {
+  const double thetaE = cl.kb * temp / (cl.me * cl.c * cl.c);
+  const double x = cl.h * nu / (cl.kb * temp);
+  const double ne = rho / cl.ep_mmw / 2.;
+  const double ni = ne;
+  return cl.ep_prefac / sqrt(thetaE) * ne * ni * jbm::exp(-x) * 1.2;
+}
+
+// Opacity::AbsorptionCoefficient (NonCGSUnits<Gray|EPBremss>)
+__device__ __forceinline__ double absorption_coeff(const Closure &cl, double rho, double temp, double nu) {
+  const double r = cl.rho_unit * rho, T = cl.temp_unit * temp, f = nu * cl.freq_unit;
+  double alpha;
+  if (cl.opacity_model == JB_OPAC_GRAY) {
+    if (cl.gray_mode == JB_GRAY_DIRECT) {
+      alpha = r * cl.kappa;
+    } else {
+      const double Bnu = planck_bnu(cl, T, f);
+      const double jnu = r * cl.kappa * Bnu;
+      alpha = robust_ratio(jnu, Bnu);
+    }
+  } else {
+    const double Bnu = planck_bnu(cl, T, f);
+    const double jnu = epbremss_jnu(cl, r, T, f);
+    alpha = robust_ratio(jnu, Bnu);
+  }
+  return alpha * cl.length_unit;
+}
+
+// Scattering::TotalScatteringCoefficient (NonCGSUnitsS<GrayS|ThomsonS>)
+__device__ __forceinline__ double scattering_coeff(const Closure &cl, double rho) {
+  const double r = cl.rho_unit * rho;
+  double alpha;
+  if (cl.scattering_model == JB_SCAT_GRAY) {
+    alpha = (r / cl.apm) * cl.sigma;
+  } else {
+    const double ne = (r / cl.apm) / 2.;
+    alpha = ne * cl.sigma_thomson;
+  }
+  return alpha * cl.length_unit;
+}
+
+// Opacity::Emissivity (frequency- and angle-integrated)
+__device__ __forceinline__ double emissivity(const Closure &cl, double rho, double temp) {
+  const double r = rho * cl.rho_unit, T = temp * cl.temp_unit;
+  double J;
+  if (cl.opacity_model == JB_OPAC_GRAY) {
+    const double B = cl.bt_num * jbm::pow4(T) / cl.bt_den;
+    J = r * cl.kappa * B;
+  } else {
+    const double thetaE = cl.kb * T / (cl.me * cl.c * cl.c);
+    const double ne = r / cl.ep_mmw / 2.;
+    const double ni = ne;
+    J = 4. * JB_PI * cl.kb * T / cl.h * cl.ep_prefac / sqrt(thetaE) * ne * ni * 1.2;
+  }
+  return J * cl.inv_emiss_unit * cl.time_unit;
+}
+
+// ---------------------------------------------------------------------------------------
+// One photon in registers while its history is advanced.
+struct Photon {
+  double x, y, z, t, vx, vy, vz;
+  int ip, jp, kp;
+};
+// The cell the photon sits in: bounds + the quantities looked up per segment.
+struct CellEnv {
+  double xl, yl, zl, xu, yu, zu;
+  double ff, aa, ss;
+};
+
+// cosine-law direction about axis 1 (transport_utils.hpp:26-39)
+__device__ __forceinline__ void face_iso_dir(const double vv, Rng &rng, double &v1, double &v2, double &v3) {
+  const double mu = sqrt(rng.drand());
+  const double nu = sqrt(1.0 - mu * mu);
+  const double phi = 2.0 * JB_PI * rng.drand();
+  double sn, cs;
+  jbm::sincos(phi, &sn, &cs);
+  v1 = vv * mu;
+  v2 = vv * nu * cs;
+  v3 = vv * nu * sn;
+}
+
+// isotropic scatter (scattering.hpp:21-29)
+__device__ __forceinline__ void scatter_iso(Rng &rng, const double vv, double &vx, double &vy, double &vz) {
+  const double mu = 2.0 * rng.drand() - 1.0;
+  const double phi = 2.0 * JB_PI * rng.drand();
+  const double stheta = sqrt(1.0 - mu * mu);
+  double sn, cs;
+  jbm::sincos(phi, &sn, &cs);
+  vx = vv * stheta * cs;
+  vy = vv * stheta * sn;
+  vz = vv * mu;
+}
+
+// Everett & Cashwell Planck sampler (planck.hpp:27-50); running sum of j^-4
+__device__ __forceinline__ double planck_energy(const Closure &cl, Rng &rng, const double sb, const double temp) {
+  const double xi0 = rng.drand();
+  const double rhs = xi0 * cl.pi4 / 90.0;
+  int l = 1;
+  double ll = 1.0;
+  double lhs = 0.0;
+  while (l < 100) {
+    const double j = (double)l;
+    lhs += 1.0 / ((j * j) * (j * j));
+    if (lhs >= rhs) {
+      ll = j;
+      break;
+    }
+    l++;
+  }
+  const double xi1 = rng.drand();
+  const double xi2 = rng.drand();
+  const double xi3 = rng.drand();
+  const double xi4 = rng.drand();
+  return -(1.0 / ll) * jbm::log(xi1 * xi2 * xi3 * xi4) * sb * temp;
+}
+
+// One IMC segment (ptcl_transport_step, transport_utils.hpp:111-160): distances to
+// effective absorption / effective scatter / census / cell faces, capped at the smallest
+// cell width; advance; nudge across a face the photon has reached.
+template <int NDIM>
+__device__ __forceinline__ void imc_step(Rng &rng, const double t_end, const CellEnv &c, const double vv,
+                                         const double dx_cell, Photon &p, bool &is_absorbed, bool &is_scattered) {
+  constexpr bool multi_d = NDIM >= 2, three_d = NDIM == 3;
+  const double rmin = DBL_MIN;
+  const double lam_abs = 1.0 / (c.ff * c.aa + rmin);
+  const double lam_sc = 1.0 / (c.ss + (1.0 - c.ff) * c.aa + rmin);
+  const double dx_abs = -lam_abs * jbm::log(rng.drand());
+  const double dx_sc = -lam_sc * jbm::log(rng.drand());
+  const double dx_end = vv * (t_end - p.t);
+  double dx_push = jbm::min2(dx_cell, dx_end);
+  if (p.vx > 0.0) {
+    dx_push = jbm::min2(dx_push, vv * (c.xu - p.x) / p.vx);
+  } else if (p.vx < 0.0) {
+    dx_push = jbm::min2(dx_push, vv * (c.xl - p.x) / p.vx);
+  }
+  if (multi_d) {
+    if (p.vy > 0.0) {
+      dx_push = jbm::min2(dx_push, vv * (c.yu - p.y) / p.vy);
+    } else if (p.vy < 0.0) {
+      dx_push = jbm::min2(dx_push, vv * (c.yl - p.y) / p.vy);
+    }
+  }
+  if (three_d) {
+    if (p.vz > 0.0) {
+      dx_push = jbm::min2(dx_push, vv * (c.zu - p.z) / p.vz);
+    } else if (p.vz < 0.0) {
+      dx_push = jbm::min2(dx_push, vv * (c.zl - p.z) / p.vz);
+    }
+  }
+  is_absorbed = ((dx_abs < dx_push) && (dx_abs < dx_sc));
+  is_scattered = (!is_absorbed && (dx_sc < dx_push));
+  const double dt_push = (is_absorbed ? dx_abs : (is_scattered ? dx_sc : dx_push)) / vv;
+  p.t += dt_push;
+  p.x += p.vx * dt_push;
+  p.y += (multi_d ? 1.0 : 0.0) * p.vy * dt_push;
+  p.z += (three_d ? 1.0 : 0.0) * p.vz * dt_push;
+  const double fdx = EPS_IMC * (c.xu - c.xl);
+  const double fdy = EPS_IMC * (c.yu - c.yl);
+  const double fdz = EPS_IMC * (c.zu - c.zl);
+  p.x = (fabs(p.x - c.xl) < fdx) ? c.xl - fdx : p.x;
+  p.x = (fabs(p.x - c.xu) < fdx) ? c.xu + fdx : p.x;
+  p.y = (multi_d && fabs(p.y - c.yl) < fdy) ? c.yl - fdy : p.y;
+  p.y = (multi_d && fabs(p.y - c.yu) < fdy) ? c.yu + fdy : p.y;
+  p.z = (three_d && fabs(p.z - c.zl) < fdz) ? c.zl - fdz : p.z;
+  p.z = (three_d && fabs(p.z - c.zu) < fdz) ? c.zu + fdz : p.z;
+}
+
+__device__ __forceinline__ bool fuzzy_eq(const double a, const double b, const double c, const double eps) {
+  return fabs(a - b) < c * eps;  // jaybenne_utils.hpp:44-49
+}
+
+// DDMC interface condition for a photon that has just arrived on a cell face from an IMC
+// region (ptcl_ddmc_albedo, transport_utils.hpp:279-397): admit with the asymptotic
+// transmission probability, otherwise send it back out with a cosine-law direction.
+__device__ __forceinline__ void albedo_face(Rng &rng, const CellEnv &c, const double vv, bool &is_rejected,
+                                            const double dcell, const double vn, const double sign_in,
+                                            const double vsample, double &v1, double &v2, double &v3,
+                                            double &coord, const double coord_out) {
+  const double Pf = (2.0 / 3.0) / ((c.aa + c.ss) * dcell + 2.0 * LAM_EXT);
+  const double P = 2.0 * Pf * (1.0 + sign_in * 1.5 * vn / vv);
+  if (rng.drand() > P) {
+    face_iso_dir(vsample, rng, v1, v2, v3);
+    coord = coord_out;
+    is_rejected = true;
+  }
+}
+template <int NDIM>
+__device__ __forceinline__ void ddmc_albedo(Rng &rng, const CellEnv &c, const double vv, Photon &p,
+                                            bool &is_rejected) {
+  constexpr bool multi_d = NDIM >= 2, three_d = NDIM == 3;
+  const double dx = c.xu - c.xl, dy = c.yu - c.yl, dz = c.zu - c.zl;
+  const double tol = 2.5 * EPS_IMC;
+  if (fuzzy_eq(p.x, c.xl, dx, tol)) {
+    albedo_face(rng, c, vv, is_rejected, dx, p.vx, +1.0, -vv, p.vx, p.vy, p.vz, p.x, c.xl - EPS_IMC * dx);
+  } else if (fuzzy_eq(p.x, c.xu, dx, tol)) {
+    albedo_face(rng, c, vv, is_rejected, dx, p.vx, -1.0, vv, p.vx, p.vy, p.vz, p.x, c.xu + EPS_IMC * dx);
+  } else if (fuzzy_eq(p.y, c.yl, dy, tol) && multi_d) {
+    albedo_face(rng, c, vv, is_rejected, dy, p.vy, +1.0, -vv, p.vy, p.vz, p.vx, p.y, c.yl - EPS_IMC * dy);
+  } else if (fuzzy_eq(p.y, c.yu, dy, tol) && multi_d) {
+    albedo_face(rng, c, vv, is_rejected, dy, p.vy, -1.0, vv, p.vy, p.vz, p.vx, p.y, c.yu + EPS_IMC * dy);
+  } else if (fuzzy_eq(p.z, c.zl, dz, tol) && three_d) {
+    albedo_face(rng, c, vv, is_rejected, dz, p.vz, +1.0, -vv, p.vz, p.vx, p.vy, p.z, c.zl - EPS_IMC * dz);
+  } else if (fuzzy_eq(p.z, c.zu, dz, tol) && three_d) {
+    albedo_face(rng, c, vv, is_rejected, dz, p.vz, -1.0, vv, p.vz, p.vx, p.vy, p.z, c.zu + EPS_IMC * dz);
+  }
+  if (!is_rejected) {
+    p.x = 0.5 * (c.xl + c.xu);
+    p.y = 0.5 * (c.yl + c.yu);
+    p.z = 0.5 * (c.zl + c.zu);
+  }
+}
+
+// One DDMC event (ptcl_ddmc_step, transport_utils.hpp:163-277): time to the next
+// absorption-or-leak event; pick absorb / one of six faces; a leak puts the photon just
+// inside the neighbour at the face centre with an outward cosine-law direction; no event
+// before census resamples position and direction inside the cell.
+template <int NDIM>
+__device__ __forceinline__ void ddmc_step(Rng &rng, const double t_end, const CellEnv &c, const double vv,
+                                          const double P[6] /* xl, yl, zl, xu, yu, zu */, Photon &p,
+                                          bool &is_absorbed) {
+  constexpr int multi_d = NDIM >= 2 ? 1 : 0, three_d = NDIM == 3 ? 1 : 0;
+  const double rmin = DBL_MIN;
+  const double eps = EPS_DDMC;
+  const double dx = c.xu - c.xl, dy = c.yu - c.yl, dz = c.zu - c.zl;
+  const double leakx_l = P[0] / dx, leakx_u = P[3] / dx;
+  const double leaky_l = P[1] / dy, leaky_u = P[4] / dy;
+  const double leakz_l = P[2] / dz, leakz_u = P[5] / dz;
+  const double leak_tot = leakx_l + leakx_u + leaky_l + leaky_u + leakz_l + leakz_u;
+  const double cdf_ddmc = c.ff * c.aa + leak_tot + rmin;
+  const double dt_ddmc = -jbm::log(rng.drand()) / (vv * cdf_ddmc);
+  const double dt_end = t_end - p.t;
+  const bool is_ddmc_event = dt_ddmc < dt_end;
+  const double dt_push = jbm::min2(dt_ddmc, dt_end);
+  p.t += dt_push;
+  if (is_ddmc_event) {
+    const double xi = cdf_ddmc * rng.drand();
+    if (xi < c.ff * c.aa) {
+      is_absorbed = true;
+    } else if (xi < c.ff * c.aa + leak_tot) {
+      const double xim = xi - c.ff * c.aa;
+      if (xim < leakx_l) {
+        p.ip -= 1;
+        p.x = c.xl - eps * dx;
+        p.y = c.yl + 0.5 * dy;
+        p.z = c.zl + 0.5 * dz;
+        face_iso_dir(-vv, rng, p.vx, p.vy, p.vz);
+      } else if (xim < leakx_l + leakx_u) {
+        p.ip += 1;
+        p.x = c.xu + eps * dx;
+        p.y = c.yl + 0.5 * dy;
+        p.z = c.zl + 0.5 * dz;
+        face_iso_dir(vv, rng, p.vx, p.vy, p.vz);
+      } else if (xim < leakx_l + leakx_u + leaky_l) {
+        p.jp -= multi_d;
+        p.y = c.yl - eps * dy;
+        p.z = c.zl + 0.5 * dz;
+        p.x = c.xl + 0.5 * dx;
+        face_iso_dir(-vv, rng, p.vy, p.vz, p.vx);
+      } else if (xim < leakx_l + leakx_u + leaky_l + leaky_u) {
+        p.jp += multi_d;
+        p.y = c.yu + eps * dy;
+        p.z = c.zl + 0.5 * dz;
+        p.x = c.xl + 0.5 * dx;
+        face_iso_dir(vv, rng, p.vy, p.vz, p.vx);
+      } else if (xim < leakx_l + leakx_u + leaky_l + leaky_u + leakz_l) {
+        p.kp -= three_d;
+        p.z = c.zl - eps * dz;
+        p.x = c.xl + 0.5 * dx;
+        p.y = c.yl + 0.5 * dy;
+        face_iso_dir(-vv, rng, p.vz, p.vx, p.vy);
+      } else if (xim <= leak_tot) {
+        p.kp += three_d;
+        p.z = c.zu + eps * dz;
+        p.x = c.xl + 0.5 * dx;
+        p.y = c.yl + 0.5 * dy;
+        face_iso_dir(vv, rng, p.vz, p.vx, p.vy);
+      }
+    }
+  } else {
+    p.z = c.zl + rng.drand() * dz;
+    p.x = c.xl + rng.drand() * dx;
+    p.y = c.yl + rng.drand() * dy;
+    const double mu = 1.0 - 2.0 * rng.drand();
+    const double nu = sqrt(1.0 - mu * mu);
+    const double phi = 2.0 * JB_PI * rng.drand();
+    double sn, cs;
+    jbm::sincos(phi, &sn, &cs);
+    p.vz = vv * mu;
+    p.vx = vv * nu * cs;
+    p.vy = vv * nu * sn;
+  }
+}
+
+// SampleFace2D / SampleFace3D (sample_ddmc_bface.cpp:24-78): pick one of the fine faces
+// that share the coarse face the photon came through, in proportion to their leakage
+// probabilities, and spread the photon over the chosen fine face.
+__device__ __forceinline__ void sample_face_2d(const int i_l, const double dx, const double P_l, const double P_u,
+                                               Rng &rng, int &i, double &x) {
+  const int i_u = i_l + 1;
+  const double xi = (P_l + P_u) * rng.drand();
+  if (xi < P_l) {
+    x -= dx * rng.drand();
+    i = i_l;
+  } else {
+    x += dx * rng.drand();
+    i = i_u;
+  }
+}
+__device__ __forceinline__ void sample_face_3d(const int i1_l, const int i2_l, const double dx1, const double dx2,
+                                               const double P_ll, const double P_lu, const double P_ul,
+                                               const double P_uu, Rng &rng, int &i1, int &i2, double &x1,
+                                               double &x2) {
+  const int i1_u = i1_l + 1, i2_u = i2_l + 1;
+  const double xi = (P_ll + P_lu + P_ul + P_uu) * rng.drand();
+  if (xi < P_ll) {
+    x1 -= dx1 * rng.drand(); i1 = i1_l;
+    x2 -= dx2 * rng.drand(); i2 = i2_l;
+  } else if (xi < P_ll + P_lu) {
+    x1 += dx1 * rng.drand(); i1 = i1_u;
+    x2 -= dx2 * rng.drand(); i2 = i2_l;
+  } else if (xi < P_ll + P_lu + P_ul) {
+    x1 -= dx1 * rng.drand(); i1 = i1_l;
+    x2 += dx2 * rng.drand(); i2 = i2_u;
+  } else {
+    x1 += dx1 * rng.drand(); i1 = i1_u;
+    x2 += dx2 * rng.drand(); i2 = i2_u;
+  }
+}
+
+}  // namespace jbd
+
+#endif  // JAYBENNE_B200_JB_DEVICE_CUH_

@@ -1,0 +1,1072 @@
+// jb_kernels.cu — hand-written CUDA kernels (sm_100a) of the jaybenne IMC/DDMC hot path.
+//
+//   k_fleck / k_face_prob     UpdateDerivedTransportFields      src/jaybenne/jaybenne.cpp:285-492
+//   k_source_count / _emit    SourcePhotons pass 1 / pass 2     src/jaybenne/sourcing.cpp:25-205
+//   k_transport               TransportPhotons(_DDMC) + the swarm boundary conditions and the
+//                             on-device meshblock hand-over     src/jaybenne/transport.cpp:28-181,
+//                             transport_ddmc.cpp:28-237, boundaries.hpp:24-84, jaybenne.cpp:26-61
+//   k_bface                   SampleDDMCBlockFace               src/jaybenne/sample_ddmc_bface.cpp:81-427
+//   k_tally                   EvaluateRadiationEnergy           src/jaybenne/jaybenne.cpp:514-564
+//   k_update_fluid            UpdateFluid                       src/jaybenne/jaybenne.cpp:583-615
+//   k_census                  CheckCompletion + census sums     src/jaybenne/transport.cpp:187-216
+//
+// Compile with -fmad=false: see jb_device.cuh.
+#include "jb_kernels.cuh"
+
+namespace jbd {
+
+// ---------------------------------------------------------------------------------------
+// small helpers
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum_f64(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  return v;
+}
+// all 32 lanes must call
+__device__ __forceinline__ void warp_add_u64(unsigned long long *dst, unsigned long long v) {
+  v = warp_sum_u64(v);
+  if ((threadIdx.x & 31) == 0 && v) atomicAdd(dst, v);
+}
+__device__ __forceinline__ void warp_add_f64(double *dst, double v) {
+  v = warp_sum_f64(v);
+  if ((threadIdx.x & 31) == 0 && v != 0.0) atomicAdd(dst, v);
+}
+
+// UniformCartesian::Xc<dir>(idx), idx given as interior index
+__device__ __forceinline__ double cell_center(const DBlock &b, const int ng, const int d, const int i) {
+  return b.xmin0[d] + ((i + ng) + 0.5) * b.dx[d];
+}
+
+__device__ __forceinline__ int lattice_at(const DMesh &m, int lx, int ly, int lz) {
+  return m.lattice[((size_t)lz * m.nlat[1] + ly) * m.nlat[0] + lx];
+}
+
+// gid of the leaf block containing pos (already inside the domain), -1 on failure.
+__device__ int find_block(const DMesh &m, const double pos[3]) {
+  int l[3] = {0, 0, 0};
+  for (int d = 0; d < m.ndim; ++d) {
+    const double w = (m.xmax[d] - m.xmin[d]) / m.nlat[d];
+    int v = (int)floor((pos[d] - m.xmin[d]) / w);
+    l[d] = min(max(v, 0), m.nlat[d] - 1);
+  }
+  for (int it = 0; it < 8; ++it) {
+    const int gid = lattice_at(m, l[0], l[1], l[2]);
+    const DBlock &b = m.blocks[gid];
+    bool ok = true;
+    for (int d = 0; d < m.ndim; ++d) {
+      const double dxd = (b.xmax[d] - b.xmin[d]) / m.nxb[d];
+      const int ii = (int)floor((pos[d] - b.xmin[d]) / dxd);
+      const int s = 1 << (m.max_level - b.level);
+      if (ii < 0) {
+        l[d] = b.lx[d] * s - 1;
+        ok = false;
+      } else if (ii >= m.nxb[d]) {
+        l[d] = (b.lx[d] + 1) * s;
+        ok = false;
+      }
+      if (l[d] < 0 || l[d] >= m.nlat[d]) return -1;
+    }
+    if (ok) return gid;
+  }
+  return -1;
+}
+
+// ---------------------------------------------------------------------------------------
+// UpdateDerivedTransportFields: Fleck factor (jaybenne.cpp:304-316)
+// ---------------------------------------------------------------------------------------
+__global__ void k_fleck(StepParams P, double dt, long long ncells) {
+  for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncells;
+       c += (long long)gridDim.x * blockDim.x) {
+    const double rho = P.f.rho[c], sie = P.f.sie[c];
+    const double temp = eos_temperature(P.cl, sie);
+    const double cv = P.cl.cv;
+    const double emis = emissivity(P.cl, rho, temp);
+    P.f.fleck[c] = 1.0 / (1.0 + (4.0 * emis / (rho * cv * temp)) * dt);
+  }
+}
+
+// value of rho (field 0) or sie (field 1) at level-L global cell G with ghost-fill
+// semantics: same level copy, coarser neighbour -> covering cell, finer neighbour -> mean
+// of the covering fine cells, outflow -> clamp, periodic -> wrap.
+__device__ double sample_cell_leaf(const StepParams &P, int field, int L, const long long Gin[3], bool &finer) {
+  const DMesh &m = P.mesh;
+  long long G[3] = {Gin[0], Gin[1], Gin[2]};
+  for (int d = 0; d < 3; ++d) {
+    const long long n = ((long long)m.nrb[d] * m.nxb[d]) << (d < m.ndim ? L : 0);
+    if (G[d] < 0 || G[d] >= n) {
+      const bool periodic = m.mesh_bc[2 * d + (G[d] < 0 ? 0 : 1)] == JB_BC_PERIODIC;
+      if (periodic) {
+        G[d] = ((G[d] % n) + n) % n;
+      } else {
+        G[d] = min(max(G[d], 0LL), n - 1);
+      }
+    }
+  }
+  int l[3] = {0, 0, 0};
+  for (int d = 0; d < m.ndim; ++d) l[d] = (int)((G[d] << (m.max_level - L)) / m.nxb[d]);
+  const int gid = lattice_at(m, l[0], l[1], l[2]);
+  const DBlock &nb = m.blocks[gid];
+  finer = false;
+  if (nb.local < 0) return jbm::mk_nan();
+  const double *f = field == 0 ? P.f.rho : P.f.sie;
+  if (nb.level <= L) {
+    int idx[3] = {0, 0, 0};
+    for (int d = 0; d < m.ndim; ++d) idx[d] = (int)((G[d] >> (L - nb.level)) - (long long)nb.lx[d] * m.nxb[d]);
+    return f[(size_t)nb.local * m.ncell + ((size_t)idx[2] * m.nxb[1] + idx[1]) * m.nxb[0] + idx[0]];
+  }
+  finer = true;
+  return 0.0;
+}
+__device__ double sample_cell(const StepParams &P, int field, int L, const long long G[3]) {
+  bool finer;
+  const double v = sample_cell_leaf(P, field, L, G, finer);
+  if (!finer) return v;
+  // wrap / clamp G first exactly like the leaf lookup did, then average the children
+  const DMesh &m = P.mesh;
+  long long Gw[3] = {G[0], G[1], G[2]};
+  for (int d = 0; d < 3; ++d) {
+    const long long n = ((long long)m.nrb[d] * m.nxb[d]) << (d < m.ndim ? L : 0);
+    if (Gw[d] < 0 || Gw[d] >= n) {
+      const bool periodic = m.mesh_bc[2 * d + (Gw[d] < 0 ? 0 : 1)] == JB_BC_PERIODIC;
+      Gw[d] = periodic ? ((Gw[d] % n) + n) % n : min(max(Gw[d], 0LL), n - 1);
+    }
+  }
+  double sum = 0.0;
+  int cnt = 0;
+  const int nk = m.ndim > 2 ? 2 : 1, nj = m.ndim > 1 ? 2 : 1;
+  for (int ck = 0; ck < nk; ++ck)
+    for (int cj = 0; cj < nj; ++cj)
+      for (int ci = 0; ci < 2; ++ci) {
+        const long long Gc[3] = {2 * Gw[0] + ci, m.ndim > 1 ? 2 * Gw[1] + cj : Gw[1],
+                                 m.ndim > 2 ? 2 * Gw[2] + ck : Gw[2]};
+        bool f2;
+        sum += sample_cell_leaf(P, field, L + 1, Gc, f2);
+        cnt++;
+      }
+  return sum / cnt;
+}
+
+// level of the leaf across face (dir, side); own level at a non-periodic domain boundary
+__device__ int neighbor_level(const DMesh &m, const DBlock &b, int dir, int side) {
+  const int s = 1 << (m.max_level - b.level);
+  int l[3];
+  for (int d = 0; d < 3; ++d) l[d] = d < m.ndim ? b.lx[d] * s : 0;
+  l[dir] = side == 0 ? b.lx[dir] * s - 1 : (b.lx[dir] + 1) * s;
+  if (l[dir] < 0 || l[dir] >= m.nlat[dir]) {
+    if (m.mesh_bc[2 * dir + side] != JB_BC_PERIODIC) return b.level;
+    l[dir] = (l[dir] + m.nlat[dir]) % m.nlat[dir];
+  }
+  return m.blocks[lattice_at(m, l[0], l[1], l[2])].level;
+}
+
+// DDMC face leakage probabilities (jaybenne.cpp:319-489), one thread per face
+__global__ void k_face_prob(StepParams P, int dir) {
+  const DMesh &m = P.mesh;
+  const long long nface = P.f.nface[dir];
+  const long long total = nface * m.nlocal;
+  int n[3] = {m.nxb[0], m.nxb[1], m.nxb[2]};
+  const int nu = n[dir];
+  n[dir] += 1;
+  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < total;
+       q += (long long)gridDim.x * blockDim.x) {
+    const int lb = (int)(q / nface);
+    const long long r = q - (long long)lb * nface;
+    const int i = (int)(r % n[0]), j = (int)((r / n[0]) % n[1]), k = (int)(r / ((long long)n[0] * n[1]));
+    const DBlock &b = m.blocks[m.local_gid[lb]];
+    const int L = b.level;
+    const int lev_l = neighbor_level(m, b, dir, 0), lev_u = neighbor_level(m, b, dir, 1);
+    const double dxd = b.dx[dir];
+    const int f[3] = {i, j, k};
+    const double dx_l = f[dir] == 0 ? ldexp(1.0, L - lev_l) * dxd : dxd;
+    const double dx_u = f[dir] == nu ? ldexp(1.0, L - lev_u) * dxd : dxd;
+    long long Gl[3], Gu[3];
+    for (int d = 0; d < 3; ++d) {
+      const long long base = d < m.ndim ? (long long)b.lx[d] * m.nxb[d] : 0;
+      Gu[d] = base + f[d];
+      Gl[d] = base + f[d] - (d == dir ? 1 : 0);
+    }
+    const double rho_l = sample_cell(P, 0, L, Gl), sie_l = sample_cell(P, 1, L, Gl);
+    const double rho_u = sample_cell(P, 0, L, Gu), sie_u = sample_cell(P, 1, L, Gu);
+    const double temp_l = eos_temperature(P.cl, sie_l);
+    const double temp_u = eos_temperature(P.cl, sie_u);
+    const double ss_l = scattering_coeff(P.cl, rho_l);
+    const double aa_l = absorption_coeff(P.cl, rho_l, temp_l, 1.0);
+    const double ss_u = scattering_coeff(P.cl, rho_u);
+    const double aa_u = absorption_coeff(P.cl, rho_u, temp_u, 1.0);
+    double tau_l = dx_l * (ss_l + aa_l);
+    double tau_u = dx_u * (ss_u + aa_u);
+    tau_l = tau_l > P.tau_ddmc ? tau_l : 2.0 * LAM_EXT;
+    tau_u = tau_u > P.tau_ddmc ? tau_u : 2.0 * LAM_EXT;
+    P.f.fp[dir][q] = 2.0 / (3.0 * (tau_l + tau_u));
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// SourcePhotons pass 1 (sourcing.cpp:73-119): per-cell source energy and stochastically
+// rounded photon count. One thread per cell of the blocks [first_local, first_local+nb).
+// ---------------------------------------------------------------------------------------
+__global__ void k_source_count(StepParams P, int first_local, long long ncells, int source_type, double dt,
+                               double npc, uint32_t call, int *cnt) {
+  const DMesh &m = P.mesh;
+  const double vv = P.cl.c_code, sb = P.cl.sb_code;
+  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < ncells;
+       q += (long long)gridDim.x * blockDim.x) {
+    const int lb = first_local + (int)(q / m.ncell);
+    const int ci = (int)(q % m.ncell);
+    const long long c = (long long)lb * m.ncell + ci;
+    const DBlock &b = m.blocks[m.local_gid[lb]];
+    const double dv = b.dx[0] * b.dx[1] * b.dx[2];
+    Rng rng;
+    rng.init((uint32_t)ci, (uint32_t)b.gid, call, 0u, P.key0, P.key1_cell);
+    const double rho = P.f.rho[c], sie = P.f.sie[c];
+    const double temp = eos_temperature(P.cl, sie);
+    double erad;
+    if (source_type == JB_SOURCE_THERMAL) {
+      erad = (4.0 * sb / vv) * jbm::pow4(temp) * dv;
+    } else {
+      const double emis = emissivity(P.cl, rho, temp);
+      erad = P.f.fleck[c] * emis * dv * dt;
+    }
+    double snpc = floor(npc);
+    snpc += ((npc - snpc) > rng.drand()) ? 1.0 : 0.0;
+    P.f.src_num[c] = snpc;
+    P.f.src_ew[c] = erad / snpc;
+    cnt[q] = (int)round(snpc);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// exclusive prefix sum of int counts into 64-bit offsets: chunk sums -> scan of chunk
+// sums (one CTA) -> per-chunk scan with the chunk offset. Replaces the reference's
+// team-scan + device->host->device bounce (sourcing.cpp:110-131).
+// ---------------------------------------------------------------------------------------
+static constexpr int SCAN_CHUNK = 2048;  // elements per CTA (256 threads x 8)
+
+__global__ void k_scan_chunk_sums(const int *in, long long n, long long *chunk_sum) {
+  __shared__ long long sh[8];
+  const long long base = (long long)blockIdx.x * SCAN_CHUNK;
+  long long s = 0;
+  for (int q = threadIdx.x; q < SCAN_CHUNK; q += blockDim.x) {
+    const long long i = base + q;
+    if (i < n) s += in[i];
+  }
+  unsigned long long v = warp_sum_u64((unsigned long long)s);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = (long long)v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long t = 0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += sh[w];
+    chunk_sum[blockIdx.x] = t;
+  }
+}
+// single CTA: in-place exclusive scan of nchunk values; writes the grand total
+__global__ void k_scan_chunk_offsets(long long *chunk_sum, long long nchunk, long long *total) {
+  __shared__ long long sh[1024];
+  __shared__ long long carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (long long base = 0; base < nchunk; base += blockDim.x) {
+    const long long i = base + threadIdx.x;
+    const long long v = i < nchunk ? chunk_sum[i] : 0;
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 1; o < (int)blockDim.x; o <<= 1) {
+      const long long a = threadIdx.x >= (unsigned)o ? sh[threadIdx.x - o] : 0;
+      __syncthreads();
+      sh[threadIdx.x] += a;
+      __syncthreads();
+    }
+    if (i < nchunk) chunk_sum[i] = carry + sh[threadIdx.x] - v;
+    __syncthreads();
+    if (threadIdx.x == 0) carry += sh[blockDim.x - 1];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *total = carry;
+}
+__global__ void k_scan_apply(const int *in, long long n, const long long *chunk_off, long long *out) {
+  // 256 threads, 8 consecutive elements each
+  __shared__ long long wsum[8];
+  const long long base = (long long)blockIdx.x * SCAN_CHUNK + (long long)threadIdx.x * 8;
+  int v[8];
+  long long s = 0;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    v[q] = (base + q < n) ? in[base + q] : 0;
+    s += v[q];
+  }
+  // inclusive scan of s across the CTA
+  long long incl = s;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const long long a = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += a;
+  }
+  if (lane == 31) wsum[wid] = incl;
+  __syncthreads();
+  long long woff = 0;
+  for (int w = 0; w < wid; ++w) woff += wsum[w];
+  long long run = chunk_off[blockIdx.x] + woff + incl - s;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    if (base + q < n) out[base + q] = run;
+    run += v[q];
+  }
+}
+
+long long scan_scratch_elems(long long n) { return (n + SCAN_CHUNK - 1) / SCAN_CHUNK + 1; }
+
+void launch_exclusive_scan(const int *cnt, long long *prefix, long long n, long long *scratch, long long *total,
+                           cudaStream_t st) {
+  const long long nchunk = (n + SCAN_CHUNK - 1) / SCAN_CHUNK;
+  k_scan_chunk_sums<<<(unsigned)nchunk, 256, 0, st>>>(cnt, n, scratch);
+  k_scan_chunk_offsets<<<1, 1024, 0, st>>>(scratch, nchunk, total);
+  k_scan_apply<<<(unsigned)nchunk, 256, 0, st>>>(cnt, n, scratch, prefix);
+}
+
+// ---------------------------------------------------------------------------------------
+// SourcePhotons pass 2 (sourcing.cpp:141-205): one warp per cell, lanes stride over the
+// cell's new photons so the SoA stores coalesce. Photon `np` (its index in the block's
+// prefix order) keys its random stream, so the result does not depend on the schedule.
+// ---------------------------------------------------------------------------------------
+__global__ void k_source_emit(StepParams P, int first_local, long long ncells, int source_type, double t_start,
+                              double dt, uint32_t call, const long long *prefix, long long slot0) {
+  const DMesh &m = P.mesh;
+  const double vv = P.cl.c_code, sb = P.cl.sb_code;
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  unsigned long long my_n = 0;
+  double my_e = 0.0;
+  for (long long q = warp0; q < ncells; q += nwarps) {
+    const int lbq = (int)(q / m.ncell);
+    const int lb = first_local + lbq;
+    const int ci = (int)(q % m.ncell);
+    const long long c = (long long)lb * m.ncell + ci;
+    const int npart = (int)round(P.f.src_num[c]);
+    const long long pglobal = prefix[q];
+    const long long pblock = prefix[(long long)lbq * m.ncell];
+    const int pstart = (int)(pglobal - pblock);
+    const double ew = P.f.src_ew[c];
+    if (lane == 0) {
+      // energy_delta is reset here and only here (sourcing.cpp:165-166), then debited
+      // serially so the sum rounds exactly as the reference's per-cell loop does
+      double dejbn = 0.0;
+      if (source_type == JB_SOURCE_EMISSION)
+        for (int np = 0; np < npart; ++np) dejbn -= ew;
+      P.f.edelta[c] = dejbn;
+    }
+    if (npart == 0) continue;
+    const DBlock &b = m.blocks[m.local_gid[lb]];
+    const int i = ci % m.nxb[0], j = (ci / m.nxb[0]) % m.nxb[1], k = ci / (m.nxb[0] * m.nxb[1]);
+    const double xi = cell_center(b, m.ng[0], 0, i), yi = cell_center(b, m.ng[1], 1, j),
+                 zi = cell_center(b, m.ng[2], 2, k);
+    const double temp = eos_temperature(P.cl, P.f.sie[c]);
+    for (int o = lane; o < npart; o += 32) {
+      const int np = pstart + o;
+      const long long slot = slot0 + pglobal + o;
+      Rng rng;
+      rng.init((uint32_t)np, (uint32_t)b.gid, call, 0u, P.key0, P.key1_particle);
+      const double x = xi + b.dx[0] * (rng.drand() - 0.5);
+      const double y = yi + b.dx[1] * (rng.drand() - 0.5);
+      const double z = zi + b.dx[2] * (rng.drand() - 0.5);
+      const double theta = jbm::acos(2.0 * rng.drand() - 1.0);
+      const double phi = 2.0 * JB_PI * rng.drand();
+      double st, ct, sp, cp;
+      jbm::sincos(theta, &st, &ct);
+      jbm::sincos(phi, &sp, &cp);
+      const double energy = planck_energy(P.cl, rng, sb, temp);
+      double tp = 0.;
+      if (source_type == JB_SOURCE_EMISSION) tp = t_start + rng.drand() * dt;
+      P.s.x[slot] = x;
+      P.s.y[slot] = y;
+      P.s.z[slot] = z;
+      P.s.vx[slot] = vv * st * cp;
+      P.s.vy[slot] = vv * st * sp;
+      P.s.vz[slot] = vv * ct;
+      P.s.e[slot] = energy;
+      P.s.w[slot] = ew;
+      P.s.t[slot] = tp;
+      P.s.loc[slot] = make_int2(lb, ci);
+      P.s.ida[slot] = make_uint2((uint32_t)np, (uint32_t)b.gid);
+      P.s.idb[slot] = make_uint2(call, rng.n);
+      my_n += 1;
+      my_e += ew;
+    }
+  }
+  warp_add_u64(&P.stats->n_sourced, my_n);
+  warp_add_f64(&P.stats->e_sourced, my_e);
+}
+
+// ---------------------------------------------------------------------------------------
+// transport
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 load_id(const Swarm &s, long long idx) {
+  const uint2 a = s.ida[idx], b = s.idb[idx];
+  return make_uint4(a.x, a.y, b.x, b.y);
+}
+// per-thread view of the meshblock a photon is in
+struct BlkReg {
+  double xmin[3], dx[3], xmin0[3], xmax[3];
+  double dx_push;
+  int gid, lb;
+};
+__device__ __forceinline__ void load_block(const DMesh &m, int gid, BlkReg &B) {
+  const DBlock &b = m.blocks[gid];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    B.xmin[d] = b.xmin[d];
+    B.xmax[d] = b.xmax[d];
+    B.dx[d] = b.dx[d];
+    B.xmin0[d] = b.xmin0[d];
+  }
+  B.dx_push = jbm::min2(B.dx[0], jbm::min2(B.dx[1], B.dx[2]));
+  B.gid = gid;
+  B.lb = b.local;
+}
+// SwarmDeviceContext::Xtoijk as interior indices; collapsed dimensions give 0
+template <int NDIM>
+__device__ __forceinline__ void xtoijk(const BlkReg &B, const Photon &p, int &i, int &j, int &k) {
+  i = (int)floor((p.x - B.xmin[0]) / B.dx[0]);
+  j = (NDIM > 1) ? (int)floor((p.y - B.xmin[1]) / B.dx[1]) : 0;
+  k = (NDIM > 2) ? (int)floor((p.z - B.xmin[2]) / B.dx[2]) : 0;
+}
+__device__ __forceinline__ bool on_block(const DMesh &m, int i, int j, int k) {
+  return i >= 0 && i < m.nxb[0] && j >= 0 && j < m.nxb[1] && k >= 0 && k < m.nxb[2];
+}
+__device__ __forceinline__ double xc(const BlkReg &B, const int ng, const int d, const int i) {
+  return B.xmin0[d] + ((i + ng) + 0.5) * B.dx[d];
+}
+
+// Swarm boundary conditions at the domain faces, applied when a photon leaves its block:
+// periodic wrap, PhotonReflectBC (boundaries.hpp:24-84) or outflow removal (false).
+template <int NDIM>
+__device__ __forceinline__ bool apply_swarm_bc(const DMesh &m, Photon &p) {
+  double *pos[3] = {&p.x, &p.y, &p.z};
+  double *vel[3] = {&p.vx, &p.vy, &p.vz};
+#pragma unroll
+  for (int d = 0; d < NDIM; ++d) {
+    const double lo = m.xmin[d], hi = m.xmax[d];
+    if (*pos[d] < lo) {
+      const int bc = m.swarm_bc[2 * d];
+      if (bc == JB_BC_PERIODIC) {
+        *pos[d] = *pos[d] + (hi - lo);
+      } else if (bc == JB_BC_REFLECT) {
+        *pos[d] = lo + (lo - *pos[d]);
+        *vel[d] = -*vel[d];
+      } else {
+        return false;
+      }
+    } else if (*pos[d] >= hi) {
+      const int bc = m.swarm_bc[2 * d + 1];
+      if (bc == JB_BC_PERIODIC) {
+        *pos[d] = *pos[d] - (hi - lo);
+      } else if (bc == JB_BC_REFLECT) {
+        if (*pos[d] > hi) {
+          *pos[d] = hi - (*pos[d] - hi);
+          *vel[d] = -*vel[d];
+        }
+      } else {
+        return false;
+      }
+    }
+  }
+  return true;
+}
+
+__device__ __forceinline__ void log_event(const StepParams &P, const uint4 &id, uint32_t draw, int kind, int gid,
+                                          const Photon &p) {
+  const unsigned long long slot = atomicAdd(P.log.count, 1ull);
+  if ((long long)slot >= P.log.cap) return;
+  jb_event e;
+  e.id_idx = id.x; e.id_gid = id.y; e.id_call = id.z;
+  e.draw = draw;
+  e.kind = kind;
+  e.block = gid;
+  e.i = p.ip; e.j = p.jp; e.k = p.kp;
+  e.reserved = 0;
+  e.t = p.t; e.x = p.x; e.y = p.y; e.z = p.z;
+  e.v0 = p.vx; e.v1 = p.vy; e.v2 = p.vz;
+  P.log.ev[slot] = e;
+}
+
+// SampleDDMCBlockFace for one photon (sample_ddmc_bface.cpp:81-427). Face-probability
+// reads one index outside the block are clamped (the reference reads exchanged ghosts).
+template <int NDIM>
+__device__ void bface_sample(const StepParams &P, const BlkReg &B, Photon &p, Rng &rng) {
+  if (NDIM < 2) return;
+  const DMesh &m = P.mesh;
+  constexpr bool three_d = NDIM > 2;
+  const double vv = P.cl.c_code;
+  const double eps = EPS10;
+  if (!(p.vx * p.vx + p.vy * p.vy + p.vz * p.vz < eps * vv * vv)) return;
+  const int n1 = m.nxb[0], n2 = m.nxb[1], n3 = m.nxb[2];
+  const double *fp0 = P.f.fp[0] + (size_t)B.lb * P.f.nface[0];
+  const double *fp1 = P.f.fp[1] + (size_t)B.lb * P.f.nface[1];
+  const double *fp2 = three_d ? P.f.fp[2] + (size_t)B.lb * P.f.nface[2] : nullptr;
+  auto clampi = [](int v, int lo, int hi) { return min(max(v, lo), hi); };
+  auto F1 = [&](int k, int j, int i) {
+    return fp0[((size_t)clampi(k, 0, n3 - 1) * n2 + clampi(j, 0, n2 - 1)) * (n1 + 1) + clampi(i, 0, n1)];
+  };
+  auto F2 = [&](int k, int j, int i) {
+    return fp1[((size_t)clampi(k, 0, n3 - 1) * (n2 + 1) + clampi(j, 0, n2)) * n1 + clampi(i, 0, n1 - 1)];
+  };
+  auto F3 = [&](int k, int j, int i) {
+    return fp2[((size_t)clampi(k, 0, n3) * n2 + clampi(j, 0, n2 - 1)) * n1 + clampi(i, 0, n1 - 1)];
+  };
+  int &ip = p.ip, &jp = p.jp, &kp = p.kp;
+  double &x = p.x, &y = p.y, &z = p.z;
+  xtoijk<NDIM>(B, p, ip, jp, kp);
+  const double dx_i = B.dx[0], dy_j = B.dx[1], dz_k = B.dx[2];
+  const double x_i = xc(B, m.ng[0], 0, ip) - 0.5 * dx_i;
+  const double y_j = xc(B, m.ng[1], 1, jp) - 0.5 * dy_j;
+  const double z_k = xc(B, m.ng[2], 2, kp) - 0.5 * dz_k;
+  const bool at_block_x_min = fuzzy_eq(x, B.xmin[0] + 2.0 * EPS_DDMC * dx_i, dx_i, eps);
+  const bool at_block_x_max = fuzzy_eq(x, B.xmax[0] - 2.0 * EPS_DDMC * dx_i, dx_i, eps);
+  const bool at_block_y_min = fuzzy_eq(y, B.xmin[1] + 2.0 * EPS_DDMC * dy_j, dy_j, eps);
+  const bool at_block_y_max = fuzzy_eq(y, B.xmax[1] - 2.0 * EPS_DDMC * dy_j, dy_j, eps);
+  const bool at_block_z_min = three_d && fuzzy_eq(z, B.xmin[2] + 2.0 * EPS_DDMC * dz_k, dz_k, eps);
+  const bool at_block_z_max = three_d && fuzzy_eq(z, B.xmax[2] - 2.0 * EPS_DDMC * dz_k, dz_k, eps);
+  if (at_block_x_min || at_block_x_max) {
+    const double dir_sgn = at_block_x_min ? 1.0 : -1.0;
+    face_iso_dir(dir_sgn * vv, rng, p.vx, p.vy, p.vz);
+    const int ip_b = at_block_x_min ? ip : ip + 1;
+    const bool at_y_edge_u = fuzzy_eq(y, y_j, dy_j, eps);
+    const bool at_y_edge_l = fuzzy_eq(y, y_j + dy_j, dy_j, eps);
+    if (!three_d) {
+      if (at_y_edge_u || at_y_edge_l) {
+        const int jp_u = at_y_edge_u ? jp : jp + 1;
+        const int jp_l = at_y_edge_u ? jp - 1 : jp;
+        sample_face_2d(jp_l, dy_j, F1(kp, jp_l, ip_b), F1(kp, jp_u, ip_b), rng, jp, y);
+      }
+    } else {
+      const bool at_z_edge_u = fuzzy_eq(z, z_k, dz_k, eps);
+      const bool at_z_edge_l = fuzzy_eq(z, z_k + dz_k, dz_k, eps);
+      if ((at_y_edge_u || at_y_edge_l) && (at_z_edge_u || at_z_edge_l)) {
+        const int jp_u = at_y_edge_u ? jp : jp + 1, jp_l = at_y_edge_u ? jp - 1 : jp;
+        const int kp_u = at_z_edge_u ? kp : kp + 1, kp_l = at_z_edge_u ? kp - 1 : kp;
+        const double Px_uu = F1(kp_u, jp_u, ip_b), Px_ul = F1(kp_u, jp_l, ip_b);
+        const double Px_lu = F1(kp_l, jp_u, ip_b), Px_ll = F1(kp_l, jp_l, ip_b);
+        sample_face_3d(jp_l, kp_l, dy_j, dz_k, Px_ll, Px_lu, Px_ul, Px_uu, rng, jp, kp, y, z);
+      }
+    }
+  } else if (at_block_y_min || at_block_y_max) {
+    const double dir_sgn = at_block_y_min ? 1.0 : -1.0;
+    face_iso_dir(dir_sgn * vv, rng, p.vy, p.vz, p.vx);
+    const int jp_b = at_block_y_min ? jp : jp + 1;
+    const bool at_x_edge_u = fuzzy_eq(x, x_i, dx_i, eps);
+    const bool at_x_edge_l = fuzzy_eq(x, x_i + dx_i, dx_i, eps);
+    if (!three_d) {
+      if (at_x_edge_u || at_x_edge_l) {
+        const int ip_u = at_x_edge_u ? ip : ip + 1;
+        const int ip_l = at_x_edge_u ? ip - 1 : ip;
+        sample_face_2d(ip_l, dx_i, F2(kp, jp_b, ip_l), F2(kp, jp_b, ip_u), rng, ip, x);
+      }
+    } else {
+      const bool at_z_edge_u = fuzzy_eq(z, z_k, dz_k, eps);
+      const bool at_z_edge_l = fuzzy_eq(z, z_k + dz_k, dz_k, eps);
+      if ((at_z_edge_u || at_z_edge_l) && (at_x_edge_u || at_x_edge_l)) {
+        const int kp_u = at_z_edge_u ? kp : kp + 1, kp_l = at_z_edge_u ? kp - 1 : kp;
+        const int ip_u = at_x_edge_u ? ip : ip + 1, ip_l = at_x_edge_u ? ip - 1 : ip;
+        const double Py_uu = F2(kp_u, jp_b, ip_u), Py_ul = F2(kp_u, jp_b, ip_l);
+        const double Py_lu = F2(kp_l, jp_b, ip_u), Py_ll = F2(kp_l, jp_b, ip_l);
+        sample_face_3d(ip_l, kp_l, dx_i, dz_k, Py_ll, Py_lu, Py_ul, Py_uu, rng, ip, kp, x, z);
+      }
+    }
+  } else if (at_block_z_min || at_block_z_max) {
+    const double dir_sgn = at_block_z_min ? 1.0 : -1.0;
+    face_iso_dir(dir_sgn * vv, rng, p.vz, p.vx, p.vy);
+    const int kp_b = at_block_z_min ? kp : kp + 1;
+    const bool at_x_edge_u = fuzzy_eq(x, x_i, dx_i, eps);
+    const bool at_x_edge_l = fuzzy_eq(x, x_i + dx_i, dx_i, eps);
+    const bool at_y_edge_u = fuzzy_eq(y, y_j, dy_j, eps);
+    const bool at_y_edge_l = fuzzy_eq(y, y_j + dy_j, dy_j, eps);
+    if ((at_x_edge_u || at_x_edge_l) && (at_y_edge_u || at_y_edge_l)) {
+      const int ip_u = at_x_edge_u ? ip : ip + 1, ip_l = at_x_edge_u ? ip - 1 : ip;
+      const int jp_u = at_y_edge_u ? jp : jp + 1, jp_l = at_y_edge_u ? jp - 1 : jp;
+      const double Pz_uu = F3(kp_b, jp_u, ip_u), Pz_ul = F3(kp_b, jp_u, ip_l);
+      const double Pz_lu = F3(kp_b, jp_l, ip_u), Pz_ll = F3(kp_b, jp_l, ip_l);
+      sample_face_3d(ip_l, jp_l, dx_i, dy_j, Pz_ll, Pz_lu, Pz_ul, Pz_uu, rng, ip, jp, x, y);
+    }
+  }
+}
+
+// The history kernel. One thread owns one photon from its current state to the first of:
+// census (t >= t_end), absorption, escape through an outflow face, or hand-over to a
+// block owned by another rank. Crossing into another block of THIS rank applies the swarm
+// boundary conditions and continues in place — the reference's break -> Send -> Receive
+// -> next transport iteration round trip (transport.cpp:149-155, jaybenne.cpp:113-131)
+// collapses to a table lookup because the photon's stream travels with it.
+template <int NDIM, bool DDMC, bool LOG>
+__global__ void __launch_bounds__(128) k_transport(StepParams P, long long first, long long n, double t_start,
+                                                   double dt) {
+  const DMesh &m = P.mesh;
+  constexpr bool multi_d = NDIM >= 2, three_d = NDIM == 3;
+  const double t_end = t_start + dt;
+  const double vv = P.cl.c_code;
+  const int nx1 = m.nxb[0], nx2 = m.nxb[1];
+  unsigned long long c_seg = 0, c_scat = 0, c_ddmc = 0, c_cross = 0, c_abs = 0, c_esc = 0, c_sent = 0, c_err = 0,
+                     c_ovf = 0;
+  double e_abs = 0.0, e_esc = 0.0;
+  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < n;
+       q += (long long)gridDim.x * blockDim.x) {
+    const long long idx = first + q;
+    int lb = P.s.loc[idx].x;
+    if (lb < 0) continue;
+    Photon p;
+    p.t = P.s.t[idx];
+    if (!(p.t < t_end)) continue;  // census photon: nothing to do (reference re-derives ijk only)
+    p.x = P.s.x[idx]; p.y = P.s.y[idx]; p.z = P.s.z[idx];
+    p.vx = P.s.vx[idx]; p.vy = P.s.vy[idx]; p.vz = P.s.vz[idx];
+    const uint4 id = load_id(P.s, idx);
+    const double ww = P.s.w[idx], ee = P.s.e[idx];
+    Rng rng;
+    rng.init(id.x, id.y, id.z, id.w, P.key0, P.key1_particle);
+    BlkReg B;
+    load_block(m, m.local_gid[lb], B);
+    xtoijk<NDIM>(B, p, p.ip, p.jp, p.kp);
+    bool gone = false;
+    while (p.t < t_end) {
+      const uint32_t draw0 = rng.n;
+      c_seg++;
+      CellEnv c;
+      {
+        const double xcen = xc(B, m.ng[0], 0, p.ip), ycen = xc(B, m.ng[1], 1, p.jp), zcen = xc(B, m.ng[2], 2, p.kp);
+        c.xl = xcen - 0.5 * B.dx[0]; c.xu = xcen + 0.5 * B.dx[0];
+        c.yl = ycen - 0.5 * B.dx[1]; c.yu = ycen + 0.5 * B.dx[1];
+        c.zl = zcen - 0.5 * B.dx[2]; c.zu = zcen + 0.5 * B.dx[2];
+      }
+      const long long ci = (long long)B.lb * m.ncell + ((long long)p.kp * nx2 + p.jp) * nx1 + p.ip;
+      const double rho = __ldg(&P.f.rho[ci]), sie = __ldg(&P.f.sie[ci]);
+      const double temp = eos_temperature(P.cl, sie);
+      c.ff = __ldg(&P.f.fleck[ci]);
+      c.ss = scattering_coeff(P.cl, rho);
+      c.aa = absorption_coeff(P.cl, rho, temp, ee);
+      bool is_absorbed = false, is_scattered = false, is_rejected = false;
+      const bool is_ddmc_step = DDMC && (B.dx_push * (c.ss + c.aa) > P.tau_ddmc);
+      if (DDMC && is_ddmc_step) {
+        c_ddmc++;
+        const double *fp0 = P.f.fp[0] + (size_t)B.lb * P.f.nface[0];
+        double Pf[6];
+        Pf[0] = fp0[((size_t)p.kp * nx2 + p.jp) * (nx1 + 1) + p.ip];
+        Pf[3] = fp0[((size_t)p.kp * nx2 + p.jp) * (nx1 + 1) + p.ip + 1];
+        if (multi_d) {
+          const double *fp1 = P.f.fp[1] + (size_t)B.lb * P.f.nface[1];
+          Pf[1] = fp1[((size_t)p.kp * (nx2 + 1) + p.jp) * nx1 + p.ip];
+          Pf[4] = fp1[((size_t)p.kp * (nx2 + 1) + p.jp + 1) * nx1 + p.ip];
+        } else {
+          Pf[1] = 0.0; Pf[4] = 0.0;
+        }
+        if (three_d) {
+          const double *fp2 = P.f.fp[2] + (size_t)B.lb * P.f.nface[2];
+          Pf[2] = fp2[((size_t)p.kp * nx2 + p.jp) * nx1 + p.ip];
+          Pf[5] = fp2[((size_t)(p.kp + 1) * nx2 + p.jp) * nx1 + p.ip];
+        } else {
+          Pf[2] = 0.0; Pf[5] = 0.0;
+        }
+        ddmc_albedo<NDIM>(rng, c, vv, p, is_rejected);
+        if (!is_rejected) ddmc_step<NDIM>(rng, t_end, c, vv, Pf, p, is_absorbed);
+      } else {
+        imc_step<NDIM>(rng, t_end, c, vv, B.dx_push, p, is_absorbed, is_scattered);
+      }
+      xtoijk<NDIM>(B, p, p.ip, p.jp, p.kp);
+      int kind = (is_ddmc_step ? JB_EV_DDMC : 0) | (is_rejected ? JB_EV_ALBEDO_REJECT : 0);
+      if (!on_block(m, p.ip, p.jp, p.kp)) {
+        if (DDMC) {
+          // zero velocity tags a DDMC photon for block-face resampling (transport_ddmc.cpp:203-211)
+          const double vmask = !(is_ddmc_step && multi_d && !is_rejected) ? 1.0 : 0.0;
+          p.vx *= vmask;
+          p.vy *= vmask;
+          p.vz *= vmask;
+        }
+        if (LOG) {
+          uint4 idn = id;
+          log_event(P, idn, draw0, kind | JB_EV_LEFT_BLOCK | (!(p.t < t_end) ? JB_EV_CENSUS : 0), B.gid, p);
+        }
+        // ---- MeshSend / MeshReceive, on device ----
+        if (!apply_swarm_bc<NDIM>(m, p)) {
+          c_esc++;
+          e_esc += ww;
+          gone = true;
+          break;
+        }
+        const double pos[3] = {p.x, p.y, p.z};
+        const int gid = find_block(m, pos);
+        if (gid < 0) {
+          c_err++;
+          gone = true;
+          break;
+        }
+        c_cross++;
+        const DBlock &nb = m.blocks[gid];
+        if (nb.rank != m.my_rank) {
+          const unsigned long long slot = atomicAdd(&P.out.count[nb.rank], 1ull);
+          if ((long long)slot < P.out.cap) {
+            ExRecord r;
+            r.x = p.x; r.y = p.y; r.z = p.z; r.t = p.t; r.w = ww; r.e = ee;
+            r.vx = p.vx; r.vy = p.vy; r.vz = p.vz;
+            r.rng[0] = id.x; r.rng[1] = id.y; r.rng[2] = id.z; r.rng[3] = rng.n;
+            r.dest_gid = gid;
+            r.pad = 0;
+            P.out.rec[(size_t)nb.rank * P.out.cap + slot] = r;
+            c_sent++;
+          } else {
+            c_ovf++;
+          }
+          gone = true;
+          break;
+        }
+        load_block(m, gid, B);
+        lb = B.lb;
+        xtoijk<NDIM>(B, p, p.ip, p.jp, p.kp);
+        if (DDMC) bface_sample<NDIM>(P, B, p, rng);
+        continue;
+      }
+      if (is_absorbed) {
+        atomicAdd(&P.f.edelta[(long long)B.lb * m.ncell + ((long long)p.kp * nx2 + p.jp) * nx1 + p.ip], ww);
+        c_abs++;
+        e_abs += ww;
+        if (LOG) log_event(P, id, draw0, kind | JB_EV_ABSORB, B.gid, p);
+        gone = true;
+        break;
+      }
+      if (is_scattered) {
+        scatter_iso(rng, vv, p.vx, p.vy, p.vz);
+        c_scat++;
+        kind |= JB_EV_SCATTER;
+      }
+      if (LOG) log_event(P, id, draw0, kind | (!(p.t < t_end) ? JB_EV_CENSUS : 0), B.gid, p);
+    }
+    if (gone) {
+      P.s.loc[idx].x = -1;
+      continue;
+    }
+    P.s.x[idx] = p.x; P.s.y[idx] = p.y; P.s.z[idx] = p.z; P.s.t[idx] = p.t;
+    P.s.vx[idx] = p.vx; P.s.vy[idx] = p.vy; P.s.vz[idx] = p.vz;
+    P.s.loc[idx] = make_int2(lb, (p.kp * nx2 + p.jp) * nx1 + p.ip);
+    P.s.idb[idx] = make_uint2(id.z, rng.n);
+  }
+  DStats *S = P.stats;
+  warp_add_u64(&S->n_segments, c_seg);
+  warp_add_u64(&S->n_scatters, c_scat);
+  warp_add_u64(&S->n_crossings, c_cross);
+  warp_add_u64(&S->n_absorbed, c_abs);
+  warp_add_u64(&S->n_dead, c_abs + c_esc + c_sent + c_err + c_ovf);
+  warp_add_f64(&S->e_absorbed, e_abs);
+  if (DDMC) warp_add_u64(&S->n_ddmc, c_ddmc);
+  // rare channels: skip the shuffles unless some lane has something
+  if (__any_sync(0xffffffffu, (c_esc | c_sent | c_err | c_ovf) != 0)) {
+    warp_add_u64(&S->n_escaped, c_esc);
+    warp_add_u64(&S->n_sent, c_sent);
+    warp_add_u64(&S->n_error, c_err);
+    warp_add_u64(&S->n_overflow, c_ovf);
+    warp_add_f64(&S->e_escaped, e_esc);
+  }
+}
+
+template <int NDIM, bool DDMC>
+static void launch_transport_nd(const StepParams &P, long long first, long long n, double t_start, double dt,
+                                cudaStream_t st) {
+  const int threads = 128;
+  long long blocks = (n + threads - 1) / threads;
+  if (blocks < 1) blocks = 1;
+  if (blocks > 0x7fffffffLL) blocks = 0x7fffffffLL;
+  if (P.log.cap > 0)
+    k_transport<NDIM, DDMC, true><<<(unsigned)blocks, threads, 0, st>>>(P, first, n, t_start, dt);
+  else
+    k_transport<NDIM, DDMC, false><<<(unsigned)blocks, threads, 0, st>>>(P, first, n, t_start, dt);
+}
+
+void launch_transport(const StepParams &P, long long first, long long n, double t_start, double dt,
+                      cudaStream_t st) {
+  if (n <= 0) return;
+  const bool dd = P.use_ddmc != 0;
+  switch (P.mesh.ndim) {
+    case 1: dd ? launch_transport_nd<1, true>(P, first, n, t_start, dt, st) : launch_transport_nd<1, false>(P, first, n, t_start, dt, st); break;
+    case 2: dd ? launch_transport_nd<2, true>(P, first, n, t_start, dt, st) : launch_transport_nd<2, false>(P, first, n, t_start, dt, st); break;
+    default: dd ? launch_transport_nd<3, true>(P, first, n, t_start, dt, st) : launch_transport_nd<3, false>(P, first, n, t_start, dt, st); break;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// SampleDDMCBlockFace over a slot range (photons that arrived from another rank)
+// ---------------------------------------------------------------------------------------
+template <int NDIM>
+__global__ void k_bface(StepParams P, long long first, long long n) {
+  const DMesh &m = P.mesh;
+  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < n;
+       q += (long long)gridDim.x * blockDim.x) {
+    const long long idx = first + q;
+    const int lb = P.s.loc[idx].x;
+    if (lb < 0) continue;
+    Photon p;
+    p.x = P.s.x[idx]; p.y = P.s.y[idx]; p.z = P.s.z[idx]; p.t = P.s.t[idx];
+    p.vx = P.s.vx[idx]; p.vy = P.s.vy[idx]; p.vz = P.s.vz[idx];
+    const double vv = P.cl.c_code;
+    if (!(p.vx * p.vx + p.vy * p.vy + p.vz * p.vz < EPS10 * vv * vv)) continue;
+    const uint4 id = load_id(P.s, idx);
+    Rng rng;
+    rng.init(id.x, id.y, id.z, id.w, P.key0, P.key1_particle);
+    BlkReg B;
+    load_block(m, m.local_gid[lb], B);
+    bface_sample<NDIM>(P, B, p, rng);
+    P.s.x[idx] = p.x; P.s.y[idx] = p.y; P.s.z[idx] = p.z;
+    P.s.vx[idx] = p.vx; P.s.vy[idx] = p.vy; P.s.vz[idx] = p.vz;
+    P.s.loc[idx].y = (p.kp * m.nxb[1] + p.jp) * m.nxb[0] + p.ip;
+    P.s.idb[idx] = make_uint2(id.z, rng.n);
+  }
+}
+static inline unsigned grid_for(long long n, int threads) {
+  long long b = (n + threads - 1) / threads;
+  if (b < 1) b = 1;
+  if (b > 148LL * 64) b = 148LL * 64;  // grid-stride beyond that: 148 SMs x 64 CTAs
+  return (unsigned)b;
+}
+void launch_bface_range(const StepParams &P, long long first, long long n, cudaStream_t st) {
+  if (n <= 0 || P.mesh.ndim < 2) return;
+  if (P.mesh.ndim == 2)
+    k_bface<2><<<grid_for(n, 128), 128, 0, st>>>(P, first, n);
+  else
+    k_bface<3><<<grid_for(n, 128), 128, 0, st>>>(P, first, n);
+}
+void launch_bface(const StepParams &P, long long n, cudaStream_t st) { launch_bface_range(P, 0, n, st); }
+
+// ---------------------------------------------------------------------------------------
+// cell-field kernels
+// ---------------------------------------------------------------------------------------
+void launch_fleck(const StepParams &P, double dt, cudaStream_t st) {
+  const long long ncells = (long long)P.mesh.nlocal * P.mesh.ncell;
+  if (ncells <= 0) return;
+  k_fleck<<<grid_for(ncells, 256), 256, 0, st>>>(P, dt, ncells);
+}
+void launch_face_prob(const StepParams &P, cudaStream_t st) {
+  for (int d = 0; d < P.mesh.ndim; ++d) {
+    const long long total = P.f.nface[d] * P.mesh.nlocal;
+    if (total > 0) k_face_prob<<<grid_for(total, 128), 128, 0, st>>>(P, d);
+  }
+}
+void launch_source_count(const StepParams &P, int first_local, int nlocal_call, int source_type, double dt,
+                         double npc, uint32_t call, int *cnt, cudaStream_t st) {
+  const long long ncells = (long long)nlocal_call * P.mesh.ncell;
+  if (ncells <= 0) return;
+  k_source_count<<<grid_for(ncells, 256), 256, 0, st>>>(P, first_local, ncells, source_type, dt, npc, call, cnt);
+}
+void launch_source_emit(const StepParams &P, int first_local, int nlocal_call, int source_type, double t_start,
+                        double dt, uint32_t call, const long long *prefix, long long slot0, cudaStream_t st) {
+  const long long ncells = (long long)nlocal_call * P.mesh.ncell;
+  if (ncells <= 0) return;
+  // one warp per cell, 8 warps per CTA
+  k_source_emit<<<grid_for(ncells * 32, 256), 256, 0, st>>>(P, first_local, ncells, source_type, t_start, dt, call,
+                                                           prefix, slot0);
+}
+
+// EvaluateRadiationEnergy (jaybenne.cpp:547-561): tally(cell) += w / dV over census photons
+__global__ void k_tally(StepParams P, long long n) {
+  const DMesh &m = P.mesh;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < n;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int2 lc = P.s.loc[idx];
+    const int lb = lc.x;
+    if (lb < 0) continue;
+    const DBlock &b = m.blocks[m.local_gid[lb]];
+    const double dv = b.dx[0] * b.dx[1] * b.dx[2];
+    atomicAdd(&P.f.tally[(long long)lb * m.ncell + lc.y], P.s.w[idx] / dv);
+  }
+}
+void launch_tally(const StepParams &P, long long n, cudaStream_t st) {
+  const long long ncells = (long long)P.mesh.nlocal * P.mesh.ncell;
+  cudaMemsetAsync(P.f.tally, 0, sizeof(double) * ncells, st);
+  if (n > 0) k_tally<<<grid_for(n, 256), 256, 0, st>>>(P, n);
+}
+
+// UpdateFluid (jaybenne.cpp:603-612): u += energy_delta / dV
+__global__ void k_update_fluid(StepParams P, long long ncells) {
+  const DMesh &m = P.mesh;
+  for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncells;
+       c += (long long)gridDim.x * blockDim.x) {
+    const DBlock &b = m.blocks[m.local_gid[(int)(c / m.ncell)]];
+    const double dv = b.dx[0] * b.dx[1] * b.dx[2];
+    const double delta = P.f.edelta[c] / dv;
+    P.f.u[c] += delta;
+  }
+}
+void launch_update_fluid(const StepParams &P, cudaStream_t st) {
+  const long long ncells = (long long)P.mesh.nlocal * P.mesh.ncell;
+  if (ncells > 0) k_update_fluid<<<grid_for(ncells, 256), 256, 0, st>>>(P, ncells);
+}
+// mcblock::UpdateDerived (mcblock.cpp:222-231): sie = u / rho
+__global__ void k_update_derived_material(StepParams P, long long ncells) {
+  for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncells;
+       c += (long long)gridDim.x * blockDim.x)
+    P.f.sie[c] = P.f.u[c] / P.f.rho[c];
+}
+void launch_update_derived_material(const StepParams &P, cudaStream_t st) {
+  const long long ncells = (long long)P.mesh.nlocal * P.mesh.ncell;
+  if (ncells > 0) k_update_derived_material<<<grid_for(ncells, 256), 256, 0, st>>>(P, ncells);
+}
+// mcblock::PostInitialization (mcblock.cpp:252-261): u = rho * sie
+__global__ void k_post_initialization(StepParams P, long long ncells) {
+  for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncells;
+       c += (long long)gridDim.x * blockDim.x)
+    P.f.u[c] = P.f.rho[c] * P.f.sie[c];
+}
+void launch_post_initialization(const StepParams &P, cudaStream_t st) {
+  const long long ncells = (long long)P.mesh.nlocal * P.mesh.ncell;
+  if (ncells > 0) k_post_initialization<<<grid_for(ncells, 256), 256, 0, st>>>(P, ncells);
+}
+
+// CheckCompletion (transport.cpp:198-209) + census sums: photons in use, photons with
+// t < t_end, and the energy they carry.
+__global__ void k_census(StepParams P, long long n, double t_end, unsigned long long *n_alive,
+                         unsigned long long *n_unfinished, double *e_sum) {
+  unsigned long long a = 0, u = 0;
+  double e = 0.0;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < n;
+       idx += (long long)gridDim.x * blockDim.x) {
+    if (P.s.loc[idx].x < 0) continue;
+    a++;
+    e += P.s.w[idx];
+    if (P.s.t[idx] < t_end) u++;
+  }
+  warp_add_u64(n_alive, a);
+  warp_add_u64(n_unfinished, u);
+  warp_add_f64(e_sum, e);
+}
+void launch_census(const StepParams &P, long long n, double t_end, unsigned long long *n_alive,
+                   unsigned long long *n_unfinished, double *e_sum, cudaStream_t st) {
+  if (n > 0) k_census<<<grid_for(n, 256), 256, 0, st>>>(P, n, t_end, n_alive, n_unfinished, e_sum);
+}
+
+// ---------------------------------------------------------------------------------------
+// compaction: slots [0, n) -> [0, n_alive). Dead slots below n_alive ("holes") are filled
+// with live photons from slots >= n_alive ("tails"); only those photons move. Order is not
+// preserved — nothing depends on it (streams are keyed per photon).
+// counters[0] = #holes, counters[1] = #tails (must be zero on entry)
+// ---------------------------------------------------------------------------------------
+__global__ void k_compact_find(StepParams P, long long n, long long n_alive, long long *holes, long long *tails,
+                               unsigned long long *counters) {
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < n;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const bool alive = P.s.loc[idx].x >= 0;
+    if (idx < n_alive) {
+      if (!alive) holes[atomicAdd(&counters[0], 1ull)] = idx;
+    } else {
+      if (alive) tails[atomicAdd(&counters[1], 1ull)] = idx;
+    }
+  }
+}
+__global__ void k_compact_move(StepParams P, const long long *holes, const long long *tails,
+                               const unsigned long long *counters) {
+  const long long nh = (long long)counters[0];
+  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < nh;
+       q += (long long)gridDim.x * blockDim.x) {
+    const long long d = holes[q], s = tails[q];
+    P.s.x[d] = P.s.x[s]; P.s.y[d] = P.s.y[s]; P.s.z[d] = P.s.z[s];
+    P.s.t[d] = P.s.t[s]; P.s.w[d] = P.s.w[s]; P.s.e[d] = P.s.e[s];
+    P.s.vx[d] = P.s.vx[s]; P.s.vy[d] = P.s.vy[s]; P.s.vz[d] = P.s.vz[s];
+    P.s.loc[d] = P.s.loc[s];
+    P.s.ida[d] = P.s.ida[s]; P.s.idb[d] = P.s.idb[s];
+    P.s.loc[s].x = -1;
+  }
+}
+void launch_compact(const StepParams &P, long long n, long long n_alive, long long *holes, long long *tails,
+                    unsigned long long *counters, cudaStream_t st) {
+  if (n <= 0 || n_alive >= n) return;
+  cudaMemsetAsync(counters, 0, 2 * sizeof(unsigned long long), st);
+  k_compact_find<<<grid_for(n, 256), 256, 0, st>>>(P, n, n_alive, holes, tails, counters);
+  const long long nmove = n - n_alive;  // upper bound on #holes
+  k_compact_move<<<grid_for(nmove, 256), 256, 0, st>>>(P, holes, tails, counters);
+}
+
+// ---------------------------------------------------------------------------------------
+// Receive side of the swarm exchange: append records to the pool (Swarm::Receive).
+// ---------------------------------------------------------------------------------------
+__global__ void k_unpack(StepParams P, const ExRecord *rec, long long nrec, long long slot0, double t_end) {
+  const DMesh &m = P.mesh;
+  unsigned long long c_unf = 0, c_err = 0, c_rcv = 0;
+  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < nrec;
+       q += (long long)gridDim.x * blockDim.x) {
+    const ExRecord r = rec[q];
+    const long long idx = slot0 + q;
+    const int gid = r.dest_gid;
+    int lb = -1;
+    if (gid >= 0 && gid < m.nblocks) lb = m.blocks[gid].local;
+    if (lb < 0) {
+      c_err++;
+      P.s.loc[idx] = make_int2(-1, 0);
+      continue;
+    }
+    const DBlock &b = m.blocks[gid];
+    const int i = (int)floor((r.x - b.xmin[0]) / b.dx[0]);
+    const int j = m.ndim > 1 ? (int)floor((r.y - b.xmin[1]) / b.dx[1]) : 0;
+    const int k = m.ndim > 2 ? (int)floor((r.z - b.xmin[2]) / b.dx[2]) : 0;
+    P.s.x[idx] = r.x; P.s.y[idx] = r.y; P.s.z[idx] = r.z; P.s.t[idx] = r.t;
+    P.s.w[idx] = r.w; P.s.e[idx] = r.e;
+    P.s.vx[idx] = r.vx; P.s.vy[idx] = r.vy; P.s.vz[idx] = r.vz;
+    P.s.loc[idx] = make_int2(lb, (k * m.nxb[1] + j) * m.nxb[0] + i);
+    P.s.ida[idx] = make_uint2(r.rng[0], r.rng[1]);
+    P.s.idb[idx] = make_uint2(r.rng[2], r.rng[3]);
+    c_rcv++;
+    if (r.t < t_end) c_unf++;
+  }
+  warp_add_u64(&P.stats->n_received, c_rcv);
+  warp_add_u64(&P.stats->n_unfinished, c_unf);
+  warp_add_u64(&P.stats->n_error, c_err);
+}
+void launch_unpack(const StepParams &P, const ExRecord *rec, long long nrec, long long slot0, double t_end,
+                   cudaStream_t st) {
+  if (nrec > 0) k_unpack<<<grid_for(nrec, 128), 128, 0, st>>>(P, rec, nrec, slot0, t_end);
+}
+
+// ---------------------------------------------------------------------------------------
+// sort photons by (block, cell): counting sort. Photons of one cell end up adjacent, so a
+// warp's cell-field loads and tally atomics hit few lines. The permutation is applied
+// array by array through one scratch array (out-of-place for 1e9 photons would not fit).
+// ---------------------------------------------------------------------------------------
+__global__ void k_sort_count(StepParams P, long long n, int *cell_count) {
+  const DMesh &m = P.mesh;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < n;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int2 lc = P.s.loc[idx];
+    if (lc.x < 0) continue;
+    atomicAdd(&cell_count[(long long)lc.x * m.ncell + lc.y], 1);
+  }
+}
+// perm[dest] = source slot
+__global__ void k_sort_perm(StepParams P, long long n, long long *cell_offset, unsigned int *perm) {
+  const DMesh &m = P.mesh;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < n;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int2 lc = P.s.loc[idx];
+    if (lc.x < 0) continue;
+    const long long d =
+        (long long)atomicAdd((unsigned long long *)&cell_offset[(long long)lc.x * m.ncell + lc.y], 1ull);
+    perm[d] = (unsigned int)idx;
+  }
+}
+template <typename T>
+__global__ void k_gather(const T *__restrict__ src, T *__restrict__ dst, const unsigned int *__restrict__ perm,
+                         long long n) {
+  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < n;
+       q += (long long)gridDim.x * blockDim.x)
+    dst[q] = src[perm[q]];
+}
+void launch_sort_keys(const StepParams &P, long long n, int *cell_count, cudaStream_t st) {
+  if (n > 0) k_sort_count<<<grid_for(n, 256), 256, 0, st>>>(P, n, cell_count);
+}
+void launch_sort_perm(const StepParams &P, long long n, long long *cell_offset, unsigned int *perm, cudaStream_t st) {
+  if (n > 0) k_sort_perm<<<grid_for(n, 256), 256, 0, st>>>(P, n, cell_offset, perm);
+}
+void launch_gather_b64(const void *src, void *dst, const unsigned int *perm, long long n, cudaStream_t st) {
+  if (n > 0)
+    k_gather<unsigned long long><<<grid_for(n, 256), 256, 0, st>>>((const unsigned long long *)src,
+                                                                  (unsigned long long *)dst, perm, n);
+}
+
+}  // namespace jbd

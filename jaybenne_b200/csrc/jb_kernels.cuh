@@ -1,0 +1,126 @@
+// jb_kernels.cuh — device data layout shared by the kernels (jb_kernels.cu) and the
+// context / C ABI (jb_lib.cu).
+//
+// HBM layout
+//   cell fields   one FP64 array per field, [local block][k][j][i] (interior cells, x1
+//                 fastest), local blocks in gid order. Face probabilities: one array per
+//                 direction, [local block][...][face].
+//   photons       structure of arrays, one slot per photon, slots [0, n) in use:
+//                 12 arrays of 8 B: 9 x FP64 (x y z t w e vx vy vz), (int32 local block,
+//                 int32 flat cell), and the 16 B stream identity as two 8 B words (birth
+//                 index, birth gid | source call, draws used) = 96 B per photon. Every
+//                 array has the same element size so one scratch array serves the cell
+//                 sort for all of them. loc.x < 0 marks a slot whose photon is gone
+//                 (absorbed, escaped or handed to another rank) until the next compaction.
+//   block table   one DBlock per GLOBAL block (every rank knows the whole mesh, as every
+//                 Parthenon rank does) + the finest-level block lattice -> gid.
+#ifndef JAYBENNE_B200_JB_KERNELS_CUH_
+#define JAYBENNE_B200_JB_KERNELS_CUH_
+
+#include "jb_device.cuh"
+
+namespace jbd {
+
+struct DBlock {
+  double xmin[3], xmax[3], dx[3];
+  double xmin0[3];  // coordinate of ghost-inclusive index 0 (UniformCartesian xmin_)
+  int level, lx[3], rank, local, gid, pad;
+};
+
+struct DMesh {
+  int ndim, nxb[3], ng[3], nlat[3], nrb[3];
+  int max_level, nblocks, nlocal, my_rank, n_ranks, ncell;
+  double xmin[3], xmax[3];
+  int swarm_bc[6], mesh_bc[6];
+  const DBlock *blocks;   // [nblocks]
+  const int *lattice;     // [nlat2][nlat1][nlat0] -> gid
+  const int *local_gid;   // [nlocal] -> gid
+};
+
+struct Fields {
+  double *rho, *sie, *u, *tally, *fleck, *src_ew, *src_num, *edelta;
+  double *fp[3];
+  long long nface[3];  // values per block of fp[d]
+};
+
+struct Swarm {
+  double *x, *y, *z, *t, *w, *e, *vx, *vy, *vz;
+  int2 *loc;   // (local block or -1 = slot free, flat interior cell)
+  uint2 *ida;  // stream identity: (birth index, birth gid)
+  uint2 *idb;  //                  (source call, draws consumed)
+};
+
+// record moved between ranks (jb_exchange_*): 96 bytes
+struct ExRecord {
+  double x, y, z, t, w, e, vx, vy, vz;
+  uint32_t rng[4];
+  int32_t dest_gid;
+  int32_t pad;
+};
+
+struct Outbox {
+  ExRecord *rec;              // [n_ranks][cap]
+  unsigned long long *count;  // [n_ranks]
+  long long cap;
+};
+
+// counters accumulated on the device during one radiation step
+struct DStats {
+  unsigned long long n_sourced, n_absorbed, n_escaped, n_sent, n_received, n_crossings;
+  unsigned long long n_segments, n_scatters, n_ddmc, n_unfinished, n_error, n_dead;
+  unsigned long long n_events, n_overflow;
+  double e_sourced, e_absorbed, e_escaped;
+};
+
+struct EventLog {
+  jb_event *ev;
+  long long cap;
+  unsigned long long *count;  // == &DStats::n_events
+};
+
+struct StepParams {
+  DMesh mesh;
+  Fields f;
+  Swarm s;
+  Closure cl;
+  Outbox out;
+  EventLog log;
+  DStats *stats;
+  uint32_t key0, key1_particle, key1_cell;
+  int use_ddmc;
+  double tau_ddmc;
+};
+
+// ---- launchers (defined in jb_kernels.cu) -----------------------------------------------
+void launch_fleck(const StepParams &P, double dt, cudaStream_t st);
+void launch_face_prob(const StepParams &P, cudaStream_t st);
+void launch_source_count(const StepParams &P, int first_local, int nlocal_call, int source_type, double dt,
+                         double npc, uint32_t call, int *cnt, cudaStream_t st);
+void launch_exclusive_scan(const int *cnt, long long *prefix, long long n, long long *scratch,
+                           long long *total, cudaStream_t st);
+long long scan_scratch_elems(long long n);
+void launch_source_emit(const StepParams &P, int first_local, int nlocal_call, int source_type, double t_start,
+                        double dt, uint32_t call, const long long *prefix, long long slot0, cudaStream_t st);
+void launch_transport(const StepParams &P, long long first, long long n, double t_start, double dt,
+                      cudaStream_t st);
+void launch_tally(const StepParams &P, long long n, cudaStream_t st);
+void launch_update_fluid(const StepParams &P, cudaStream_t st);
+void launch_update_derived_material(const StepParams &P, cudaStream_t st);
+void launch_post_initialization(const StepParams &P, cudaStream_t st);
+void launch_census(const StepParams &P, long long n, double t_end, unsigned long long *n_alive,
+                   unsigned long long *n_unfinished, double *e_sum, cudaStream_t st);
+// unstable compaction of slots [0, n): returns nothing; n_alive must be known (host)
+void launch_compact(const StepParams &P, long long n, long long n_alive, long long *holes, long long *tails,
+                    unsigned long long *counters, cudaStream_t st);
+void launch_unpack(const StepParams &P, const ExRecord *rec, long long nrec, long long slot0, double t_end,
+                   cudaStream_t st);
+void launch_bface(const StepParams &P, long long n, cudaStream_t st);
+void launch_bface_range(const StepParams &P, long long first, long long n, cudaStream_t st);
+// cell sort: key = blk * ncell + cell
+void launch_sort_keys(const StepParams &P, long long n, int *cell_count, cudaStream_t st);
+void launch_sort_perm(const StepParams &P, long long n, long long *cell_offset, unsigned int *perm, cudaStream_t st);
+void launch_gather_b64(const void *src, void *dst, const unsigned int *perm, long long n, cudaStream_t st);
+
+}  // namespace jbd
+
+#endif  // JAYBENNE_B200_JB_KERNELS_CUH_

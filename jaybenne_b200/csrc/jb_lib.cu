@@ -1,0 +1,1144 @@
+// jb_lib.cu — the context behind the C ABI of include/jaybenne_b200.h: owns all device
+// memory, orders the kernels of one radiation step the way RadiationStep's task list does
+// (src/jaybenne/jaybenne.cpp:68-151) and moves photons between ranks (NCCL), replacing
+// Parthenon's swarm Send/Receive.
+//
+// There is no CPU path in this file: without a CUDA device every compute entry point
+// returns JB_ERR_NO_DEVICE.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "jb_kernels.cuh"
+
+using namespace jbd;
+
+// ---- NCCL, bound at run time so the library loads on machines without it -----------------
+struct NcclApi {
+  void *handle = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                            cudaStream_t) = nullptr;
+  ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+  bool ok = false;
+};
+static NcclApi &nccl_api() {
+  static NcclApi api;
+  if (api.handle) return api;
+  // a libnccl already in the process (e.g. the one torch ships) is reused by soname
+  api.handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!api.handle) api.handle = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  if (!api.handle) return api;
+#define JB_SYM(name) *(void **)(&api.name) = dlsym(api.handle, "nccl" #name)
+  JB_SYM(GetUniqueId); JB_SYM(CommInitRank); JB_SYM(CommDestroy); JB_SYM(AllGather); JB_SYM(AllReduce);
+  JB_SYM(Send); JB_SYM(Recv); JB_SYM(GroupStart); JB_SYM(GroupEnd); JB_SYM(GetErrorString);
+#undef JB_SYM
+  api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.AllReduce && api.Send &&
+           api.Recv && api.GroupStart && api.GroupEnd;
+  return api;
+}
+
+struct jb_ctx {
+  jb_config cfg;
+  Closure cl;
+  jb_mesh mesh;
+  std::vector<jb_block> all_blocks;
+  std::vector<int> gid_to_local, local_gid;
+  int nlat[3] = {1, 1, 1}, ng[3] = {0, 0, 0};
+  int my_rank = 0, n_ranks = 1;
+  bool mesh_set = false;
+  int device = -1;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+
+  // device tables
+  DBlock *d_blocks = nullptr;
+  int *d_lattice = nullptr, *d_local_gid = nullptr;
+  Fields f{};
+  long long ncells_local = 0;
+  Swarm s{};
+  long long capacity = 0, n = 0;
+  long long requested_capacity = 0;
+  // scratch
+  double *d_tmp = nullptr;            // one SoA-array-sized scratch: rotates with the arrays in the cell sort
+  unsigned int *d_perm = nullptr;     // sort permutation
+  int *d_cnt = nullptr;               // per-cell counts
+  long long *d_prefix = nullptr;      // per-cell offsets
+  long long *d_scan = nullptr, *d_total = nullptr;
+  long long *d_holes = nullptr, *d_tails = nullptr;
+  long long holes_cap = 0;
+  unsigned long long *d_counters = nullptr;  // [8] misc device counters
+  double *d_esum = nullptr;
+  DStats *d_stats = nullptr;
+  DStats *h_stats = nullptr;          // pinned
+  unsigned long long *h_counters = nullptr;  // pinned [8 + n_ranks*n_ranks]
+  // exchange
+  Outbox out{};
+  ExRecord *d_inbox = nullptr;
+  long long inbox_cap = 0;
+  unsigned long long *d_count_matrix = nullptr;
+  ncclComm_t comm = nullptr;
+  // event log
+  jb_event *d_events = nullptr;
+  long long event_cap = 0;
+
+  uint32_t source_call = 0;
+  int cycles_since_sort = 0;
+  jb_cycle_stats stats;
+  long long launches = 0;             // kernels launched since creation (bench: gpu_launches)
+  std::string err;
+};
+
+static jb_status fail(jb_ctx *c, jb_status s, const std::string &m) {
+  if (c) c->err = m;
+  return s;
+}
+#define JB_CUDA(c, call)                                                                         \
+  do {                                                                                           \
+    cudaError_t e_ = (call);                                                                     \
+    if (e_ != cudaSuccess)                                                                       \
+      return fail((c), JB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));         \
+  } while (0)
+
+template <typename T>
+static cudaError_t dalloc(T **p, long long nelem) {
+  *p = nullptr;
+  if (nelem <= 0) nelem = 1;
+  return cudaMalloc((void **)p, sizeof(T) * (size_t)nelem);
+}
+static void dfree(void *p) {
+  if (p) cudaFree(p);
+}
+
+// CGS constants as singularity-opac derives them (constants/constants.hpp:41-178)
+namespace cgs {
+static constexpr double length = 1.e2, mass = 1.e3, time = 1., temperature = 1.;
+static constexpr double force = mass * length / (time * time);
+static constexpr double energy = force * length;
+static constexpr double h = 6.62606957e-34 * energy * time;
+static constexpr double kb = 1.380648800e-23 * energy / temperature;
+static constexpr double c = 2.99792458e8 * length / time;
+static constexpr double sb = 2.0 * M_PI * M_PI * M_PI * M_PI * M_PI * kb * kb * kb * kb / (15.0 * h * h * h * c * c);
+static constexpr double me = 9.10938291e-31 * mass;
+static constexpr double mp = 1.672621777e-27 * mass;
+static constexpr double alpha = 7.2973525698e-3;
+static constexpr double hbar = h / (2.0 * M_PI);
+static constexpr double qe = 1.602176565e-19 * 2.997924580e9;
+}  // namespace cgs
+
+// Flatten the closures mcblock builds (mcblock.cpp:78-143) into numbers; the derived
+// constants follow non_cgs_photons.hpp:33-46 and constants.hpp:191-207.
+static void make_closure(const jb_config &c, Closure &cl) {
+  memset(&cl, 0, sizeof(cl));
+  cl.opacity_model = c.opacity_model;
+  cl.scattering_model = c.scattering_model;
+  cl.gray_mode = c.gray_mode;
+  cl.kappa = c.opacity_kappa;
+  cl.sigma = c.scattering_sigma;
+  cl.apm = c.apm;
+  cl.cv = c.eos_cv;
+  cl.time_unit = c.time_scale;
+  cl.length_unit = c.length_scale;
+  cl.temp_unit = c.temperature_scale;
+  const double mass_unit = c.mass_scale;
+  cl.rho_unit = mass_unit / (cl.length_unit * cl.length_unit * cl.length_unit);
+  cl.freq_unit = 1. / cl.time_unit;
+  cl.inv_emiss_unit = cl.length_unit * cl.time_unit * cl.time_unit / mass_unit;
+  cl.c_code = cgs::c * cl.time_unit / cl.length_unit;
+  cl.sb_code = cgs::sb * std::pow(cl.time_unit, 3) / mass_unit * std::pow(cl.temp_unit, 4);
+  cl.bt_num = 8. * std::pow(M_PI, 5) * std::pow(cgs::kb, 4);
+  cl.bt_den = 15. * std::pow(cgs::c, 2) * std::pow(cgs::h, 3);
+  cl.sigma_thomson = 8. * M_PI / 3. * std::pow(cgs::alpha * cgs::hbar / (cgs::me * cgs::c), 2);
+  cl.ep_mmw = (cgs::mp + cgs::me) / 2.;
+  cl.ep_prefac = 8. * std::pow(cgs::qe, 6) / (3. * std::pow(cgs::me * cgs::c * cgs::c, 2)) * std::sqrt(2. * M_PI / 3.);
+  cl.h = cgs::h;
+  cl.kb = cgs::kb;
+  cl.c = cgs::c;
+  cl.me = cgs::me;
+  cl.two_h_over_c2 = 2. * cgs::h / (cgs::c * cgs::c);
+  cl.pi4 = std::pow(M_PI, 4.0);
+}
+
+static StepParams make_params(jb_ctx *c) {
+  StepParams P;
+  memset(&P, 0, sizeof(P));
+  DMesh &m = P.mesh;
+  m.ndim = c->mesh.ndim;
+  for (int d = 0; d < 3; ++d) {
+    m.nxb[d] = c->mesh.nxb[d];
+    m.ng[d] = c->ng[d];
+    m.nlat[d] = c->nlat[d];
+    m.nrb[d] = c->mesh.nrb[d];
+    m.xmin[d] = c->mesh.xmin[d];
+    m.xmax[d] = c->mesh.xmax[d];
+  }
+  for (int q = 0; q < 6; ++q) {
+    m.swarm_bc[q] = c->mesh.swarm_bc[q];
+    m.mesh_bc[q] = c->mesh.mesh_bc[q];
+  }
+  m.max_level = c->mesh.max_level;
+  m.nblocks = c->mesh.nblocks;
+  m.nlocal = (int)c->local_gid.size();
+  m.my_rank = c->my_rank;
+  m.n_ranks = c->n_ranks;
+  m.ncell = c->mesh.nxb[0] * c->mesh.nxb[1] * c->mesh.nxb[2];
+  m.blocks = c->d_blocks;
+  m.lattice = c->d_lattice;
+  m.local_gid = c->d_local_gid;
+  P.f = c->f;
+  P.s = c->s;
+  P.cl = c->cl;
+  P.out = c->out;
+  P.log.ev = c->d_events;
+  P.log.cap = c->event_cap;
+  P.log.count = c->d_stats ? &c->d_stats->n_events : nullptr;
+  P.stats = c->d_stats;
+  P.key0 = (uint32_t)((uint64_t)c->cfg.seed);
+  P.key1_particle = (uint32_t)((uint64_t)c->cfg.seed >> 32) ^ STREAM_PARTICLE;
+  P.key1_cell = (uint32_t)((uint64_t)c->cfg.seed >> 32) ^ STREAM_CELL;
+  P.use_ddmc = c->cfg.use_ddmc;
+  P.tau_ddmc = c->cfg.tau_ddmc;
+  return P;
+}
+
+// the 12 SoA arrays, all 8 bytes per slot
+static void swarm_arrays(Swarm &s, void **out[12]) {
+  out[0] = (void **)&s.x; out[1] = (void **)&s.y; out[2] = (void **)&s.z; out[3] = (void **)&s.t;
+  out[4] = (void **)&s.w; out[5] = (void **)&s.e; out[6] = (void **)&s.vx; out[7] = (void **)&s.vy;
+  out[8] = (void **)&s.vz; out[9] = (void **)&s.loc; out[10] = (void **)&s.ida; out[11] = (void **)&s.idb;
+}
+
+static void free_swarm(jb_ctx *c) {
+  void **arr[12];
+  swarm_arrays(c->s, arr);
+  for (auto a : arr) dfree(*a);
+  dfree(c->d_tmp); dfree(c->d_perm);
+  dfree(c->out.rec); dfree(c->out.count); dfree(c->d_inbox);
+  memset(&c->s, 0, sizeof(c->s));
+  memset(&c->out, 0, sizeof(c->out));
+  c->d_tmp = nullptr;
+  c->d_perm = nullptr;
+  c->d_inbox = nullptr;
+  c->capacity = 0;
+  c->inbox_cap = 0;
+}
+
+// (re)allocate the photon pool; existing photons are preserved
+static jb_status ensure_capacity(jb_ctx *c, long long need) {
+  if (need <= c->capacity) return JB_OK;
+  long long cap = std::max(need, c->requested_capacity);
+  if (c->requested_capacity <= 0) cap = std::max<long long>(need + need / 4, 1024);
+  Swarm ns{};
+  void **na[12], **oa[12];
+  swarm_arrays(ns, na);
+  swarm_arrays(c->s, oa);
+  for (int q = 0; q < 12; ++q) {
+    JB_CUDA(c, dalloc((unsigned long long **)na[q], cap));
+    if (c->n > 0)
+      JB_CUDA(c, cudaMemcpyAsync(*na[q], *oa[q], (size_t)c->n * 8, cudaMemcpyDeviceToDevice, c->stream));
+  }
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  const long long keep_n = c->n;
+  free_swarm(c);
+  c->s = ns;
+  c->n = keep_n;
+  c->capacity = cap;
+  JB_CUDA(c, dalloc(&c->d_tmp, cap));
+  JB_CUDA(c, dalloc(&c->d_perm, cap));
+  if (c->n_ranks > 1) {
+    c->out.cap = std::max<long long>(cap / (2 * c->n_ranks), 4096);
+    JB_CUDA(c, dalloc(&c->out.rec, c->out.cap * c->n_ranks));
+    c->inbox_cap = c->out.cap * c->n_ranks;
+    JB_CUDA(c, dalloc(&c->d_inbox, c->inbox_cap));
+  }
+  JB_CUDA(c, dalloc(&c->out.count, std::max(c->n_ranks, 1)));
+  JB_CUDA(c, cudaMemset(c->out.count, 0, sizeof(unsigned long long) * std::max(c->n_ranks, 1)));
+  return JB_OK;
+}
+
+// =======================================================================================
+// C ABI
+// =======================================================================================
+extern "C" {
+
+jb_status jb_create(const jb_config *cfg, jb_ctx **out) {
+  if (!cfg || !out) return JB_ERR_INVALID;
+  *out = nullptr;
+  // jaybenne::Initialize input checks (jaybenne.cpp:171-172)
+  if (!(cfg->min_swarm_occupancy >= 0 && cfg->min_swarm_occupancy < 1.0)) return JB_ERR_INVALID;
+  if (cfg->rng_mode != JB_RNG_PHILOX) return JB_ERR_UNSUPPORTED;  // the pool generator is oracle-only
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+    cudaGetLastError();
+    return JB_ERR_NO_DEVICE;
+  }
+  jb_ctx *c = new jb_ctx();
+  c->cfg = *cfg;
+  make_closure(*cfg, c->cl);
+  memset(&c->stats, 0, sizeof(c->stats));
+  memset(&c->mesh, 0, sizeof(c->mesh));
+  if (cudaGetDevice(&c->device) != cudaSuccess || cudaStreamCreate(&c->stream) != cudaSuccess) {
+    delete c;
+    return JB_ERR_CUDA;
+  }
+  for (auto &e : c->ev) cudaEventCreate(&e);
+  bool ok = dalloc(&c->d_stats, 1) == cudaSuccess && dalloc(&c->d_counters, 8) == cudaSuccess &&
+            dalloc(&c->d_esum, 2) == cudaSuccess && dalloc(&c->d_total, 2) == cudaSuccess &&
+            cudaMallocHost((void **)&c->h_stats, sizeof(DStats)) == cudaSuccess &&
+            cudaMallocHost((void **)&c->h_counters, sizeof(unsigned long long) * (16 + 64 * 64)) == cudaSuccess;
+  if (!ok) {
+    delete c;
+    return JB_ERR_CUDA;
+  }
+  cudaMemset(c->d_stats, 0, sizeof(DStats));
+  *out = c;
+  return JB_OK;
+}
+
+void jb_destroy(jb_ctx *c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  if (c->comm && nccl_api().ok) nccl_api().CommDestroy(c->comm);
+  free_swarm(c);
+  dfree(c->d_blocks); dfree(c->d_lattice); dfree(c->d_local_gid);
+  dfree(c->f.rho); dfree(c->f.sie); dfree(c->f.u); dfree(c->f.tally); dfree(c->f.fleck);
+  dfree(c->f.src_ew); dfree(c->f.src_num); dfree(c->f.edelta);
+  for (int d = 0; d < 3; ++d) dfree(c->f.fp[d]);
+  dfree(c->d_cnt); dfree(c->d_prefix); dfree(c->d_scan); dfree(c->d_total);
+  dfree(c->d_holes); dfree(c->d_tails); dfree(c->d_counters); dfree(c->d_esum); dfree(c->d_stats);
+  dfree(c->d_count_matrix); dfree(c->d_events);
+  if (c->h_stats) cudaFreeHost(c->h_stats);
+  if (c->h_counters) cudaFreeHost(c->h_counters);
+  for (auto &e : c->ev)
+    if (e) cudaEventDestroy(e);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+const char *jb_last_error(const jb_ctx *c) { return c ? c->err.c_str() : "null context"; }
+
+jb_status jb_get_constants(const jb_ctx *c, double *sol, double *sb) {
+  if (!c) return JB_ERR_INVALID;
+  if (sol) *sol = c->cl.c_code;
+  if (sb) *sb = c->cl.sb_code;
+  return JB_OK;
+}
+
+int64_t jb_field_size(const jb_ctx *c, int32_t field) {
+  const int64_t n1 = c->mesh.nxb[0], n2 = c->mesh.nxb[1], n3 = c->mesh.nxb[2];
+  if (field == JB_FIELD_DDMC_FACE_PROB_X1) return (n1 + 1) * n2 * n3;
+  if (field == JB_FIELD_DDMC_FACE_PROB_X2) return n1 * (n2 + 1) * n3;
+  if (field == JB_FIELD_DDMC_FACE_PROB_X3) return n1 * n2 * (n3 + 1);
+  return n1 * n2 * n3;
+}
+
+jb_status jb_set_mesh(jb_ctx *c, const jb_mesh *m, int32_t my_rank, int32_t n_ranks) {
+  if (!c) return JB_ERR_INVALID;
+  if (!m || m->nblocks <= 0 || m->ndim < 1 || m->ndim > 3) return fail(c, JB_ERR_INVALID, "bad mesh");
+  if (n_ranks < 1 || n_ranks > 64 || my_rank < 0 || my_rank >= n_ranks) return fail(c, JB_ERR_INVALID, "bad rank");
+  if (c->mesh_set) return fail(c, JB_ERR_STATE, "mesh already set");
+  JB_CUDA(c, cudaSetDevice(c->device));
+  c->mesh = *m;
+  c->all_blocks.assign(m->blocks, m->blocks + m->nblocks);
+  c->mesh.blocks = c->all_blocks.data();
+  c->my_rank = my_rank;
+  c->n_ranks = n_ranks;
+  for (int d = 0; d < 3; ++d) {
+    c->nlat[d] = d < m->ndim ? (m->nrb[d] << m->max_level) : 1;
+    c->ng[d] = (d < m->ndim) ? m->nghost : 0;
+  }
+  std::vector<int> lattice((size_t)c->nlat[0] * c->nlat[1] * c->nlat[2], -1);
+  c->gid_to_local.assign(m->nblocks, -1);
+  c->local_gid.clear();
+  std::vector<DBlock> hb(m->nblocks);
+  for (int g = 0; g < m->nblocks; ++g) {
+    const jb_block &b = c->all_blocks[g];
+    if (b.gid != g) return fail(c, JB_ERR_INVALID, "blocks must be listed in gid order");
+    if (b.level < 0 || b.level > m->max_level) return fail(c, JB_ERR_INVALID, "block level out of range");
+    const int s = 1 << (m->max_level - b.level);
+    int lo[3] = {0, 0, 0}, hi[3] = {1, 1, 1};
+    for (int d = 0; d < m->ndim; ++d) {
+      lo[d] = (int)b.lx[d] * s;
+      hi[d] = lo[d] + s;
+      if (lo[d] < 0 || hi[d] > c->nlat[d]) return fail(c, JB_ERR_INVALID, "block outside the root grid");
+    }
+    for (int z = lo[2]; z < hi[2]; ++z)
+      for (int y = lo[1]; y < hi[1]; ++y)
+        for (int x = lo[0]; x < hi[0]; ++x) lattice[((size_t)z * c->nlat[1] + y) * c->nlat[0] + x] = g;
+    DBlock &D = hb[g];
+    memset(&D, 0, sizeof(D));
+    for (int d = 0; d < 3; ++d) {
+      D.xmin[d] = b.xmin[d];
+      D.xmax[d] = b.xmax[d];
+      D.dx[d] = (b.xmax[d] - b.xmin[d]) / m->nxb[d];
+      D.xmin0[d] = b.xmin[d] - c->ng[d] * D.dx[d];
+      D.lx[d] = (int)b.lx[d];
+    }
+    D.level = b.level;
+    D.rank = b.rank;
+    D.gid = g;
+    D.local = -1;
+    if (b.rank == my_rank) {
+      D.local = (int)c->local_gid.size();
+      c->gid_to_local[g] = D.local;
+      c->local_gid.push_back(g);
+    }
+  }
+  for (int v : lattice)
+    if (v < 0) return fail(c, JB_ERR_INVALID, "block table does not tile the domain");
+  const long long nc = (long long)m->nxb[0] * m->nxb[1] * m->nxb[2];
+  const long long nl = (long long)c->local_gid.size();
+  c->ncells_local = nc * nl;
+  JB_CUDA(c, dalloc(&c->d_blocks, m->nblocks));
+  JB_CUDA(c, dalloc(&c->d_lattice, (long long)lattice.size()));
+  JB_CUDA(c, dalloc(&c->d_local_gid, nl));
+  JB_CUDA(c, cudaMemcpy(c->d_blocks, hb.data(), sizeof(DBlock) * hb.size(), cudaMemcpyHostToDevice));
+  JB_CUDA(c, cudaMemcpy(c->d_lattice, lattice.data(), sizeof(int) * lattice.size(), cudaMemcpyHostToDevice));
+  if (nl > 0)
+    JB_CUDA(c, cudaMemcpy(c->d_local_gid, c->local_gid.data(), sizeof(int) * nl, cudaMemcpyHostToDevice));
+  double **cellf[8] = {&c->f.rho, &c->f.sie, &c->f.u, &c->f.tally, &c->f.fleck, &c->f.src_ew, &c->f.src_num, &c->f.edelta};
+  for (auto pp : cellf) {
+    JB_CUDA(c, dalloc(pp, c->ncells_local));
+    JB_CUDA(c, cudaMemset(*pp, 0, sizeof(double) * (size_t)std::max<long long>(c->ncells_local, 1)));
+  }
+  c->f.nface[0] = (long long)(m->nxb[0] + 1) * m->nxb[1] * m->nxb[2];
+  c->f.nface[1] = (long long)m->nxb[0] * (m->nxb[1] + 1) * m->nxb[2];
+  c->f.nface[2] = (long long)m->nxb[0] * m->nxb[1] * (m->nxb[2] + 1);
+  if (c->cfg.use_ddmc) {
+    for (int d = 0; d < 3; ++d) {
+      JB_CUDA(c, dalloc(&c->f.fp[d], c->f.nface[d] * nl));
+      JB_CUDA(c, cudaMemset(c->f.fp[d], 0, sizeof(double) * (size_t)std::max<long long>(c->f.nface[d] * nl, 1)));
+    }
+  }
+  JB_CUDA(c, dalloc(&c->d_cnt, c->ncells_local));
+  JB_CUDA(c, dalloc(&c->d_prefix, c->ncells_local + 1));
+  JB_CUDA(c, dalloc(&c->d_scan, scan_scratch_elems(std::max<long long>(c->ncells_local, 1))));
+  JB_CUDA(c, dalloc(&c->d_count_matrix, (long long)n_ranks * n_ranks));
+  c->mesh_set = true;
+  return JB_OK;
+}
+
+jb_status jb_set_capacity(jb_ctx *c, int64_t max_particles) {
+  if (!c || max_particles < 0) return JB_ERR_INVALID;
+  if (!c->mesh_set) return fail(c, JB_ERR_STATE, "mesh not set");
+  JB_CUDA(c, cudaSetDevice(c->device));
+  c->requested_capacity = max_particles;
+  return ensure_capacity(c, max_particles);
+}
+
+static double *field_ptr(jb_ctx *c, int field, long long *per_block) {
+  *per_block = jb_field_size(c, field);
+  switch (field) {
+    case JB_FIELD_DENSITY: return c->f.rho;
+    case JB_FIELD_SIE: return c->f.sie;
+    case JB_FIELD_INTERNAL_ENERGY: return c->f.u;
+    case JB_FIELD_ENERGY_TALLY: return c->f.tally;
+    case JB_FIELD_FLECK_FACTOR: return c->f.fleck;
+    case JB_FIELD_SOURCE_EW_PER_CELL: return c->f.src_ew;
+    case JB_FIELD_SOURCE_NUM_PER_CELL: return c->f.src_num;
+    case JB_FIELD_ENERGY_DELTA: return c->f.edelta;
+    case JB_FIELD_DDMC_FACE_PROB_X1: return c->f.fp[0];
+    case JB_FIELD_DDMC_FACE_PROB_X2: return c->f.fp[1];
+    case JB_FIELD_DDMC_FACE_PROB_X3: return c->f.fp[2];
+  }
+  return nullptr;
+}
+
+jb_status jb_set_field(jb_ctx *c, int32_t gid, int32_t field, const double *src) {
+  if (!c || !src) return JB_ERR_INVALID;
+  if (!c->mesh_set) return fail(c, JB_ERR_STATE, "mesh not set");
+  if (gid < 0 || gid >= c->mesh.nblocks || c->gid_to_local[gid] < 0) return fail(c, JB_ERR_INVALID, "block not local");
+  long long nb;
+  double *p = field_ptr(c, field, &nb);
+  if (!p) return fail(c, JB_ERR_INVALID, "bad field (face probabilities exist only with use_ddmc)");
+  JB_CUDA(c, cudaSetDevice(c->device));
+  JB_CUDA(c, cudaMemcpyAsync(p + (size_t)c->gid_to_local[gid] * nb, src, sizeof(double) * nb, cudaMemcpyDefault, c->stream));
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return JB_OK;
+}
+jb_status jb_get_field(jb_ctx *c, int32_t gid, int32_t field, double *dst) {
+  if (!c || !dst) return JB_ERR_INVALID;
+  if (!c->mesh_set) return fail(c, JB_ERR_STATE, "mesh not set");
+  if (gid < 0 || gid >= c->mesh.nblocks || c->gid_to_local[gid] < 0) return fail(c, JB_ERR_INVALID, "block not local");
+  long long nb;
+  double *p = field_ptr(c, field, &nb);
+  JB_CUDA(c, cudaSetDevice(c->device));
+  if (!p) {
+    memset(dst, 0, sizeof(double) * nb);
+    return JB_OK;
+  }
+  JB_CUDA(c, cudaMemcpyAsync(dst, p + (size_t)c->gid_to_local[gid] * nb, sizeof(double) * nb, cudaMemcpyDefault, c->stream));
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return JB_OK;
+}
+
+// ---- internals of the step ---------------------------------------------------------------
+static jb_status sync_stats(jb_ctx *c) {
+  JB_CUDA(c, cudaMemcpyAsync(c->h_stats, c->d_stats, sizeof(DStats), cudaMemcpyDeviceToHost, c->stream));
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return JB_OK;
+}
+
+// census: photons in use / unfinished / energy over slots [0, n)
+static jb_status census(jb_ctx *c, double t_end, long long *n_alive, long long *n_unfinished, double *e_sum) {
+  StepParams P = make_params(c);
+  JB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * 2, c->stream));
+  JB_CUDA(c, cudaMemsetAsync(c->d_esum, 0, sizeof(double), c->stream));
+  launch_census(P, c->n, t_end, c->d_counters, c->d_counters + 1, c->d_esum, c->stream);
+  c->launches += c->n > 0;
+  JB_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(unsigned long long) * 2, cudaMemcpyDeviceToHost, c->stream));
+  JB_CUDA(c, cudaMemcpyAsync(c->h_counters + 2, c->d_esum, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (n_alive) *n_alive = (long long)c->h_counters[0];
+  if (n_unfinished) *n_unfinished = (long long)c->h_counters[1];
+  if (e_sum) memcpy(e_sum, c->h_counters + 2, sizeof(double));
+  return JB_OK;
+}
+
+// squeeze out the slots whose photon is gone; needs h_stats->n_dead to be current
+static jb_status compact(jb_ctx *c, long long n_dead) {
+  if (n_dead <= 0) return JB_OK;
+  const long long n_alive = c->n - n_dead;
+  if (n_alive < 0) return fail(c, JB_ERR_STATE, "photon bookkeeping went negative");
+  if (n_alive == 0) {
+    c->n = 0;
+    return JB_OK;
+  }
+  const long long need = std::min(n_dead, n_alive);
+  if (need > c->holes_cap) {
+    dfree(c->d_holes);
+    dfree(c->d_tails);
+    c->holes_cap = need + need / 4 + 1024;
+    JB_CUDA(c, dalloc(&c->d_holes, c->holes_cap));
+    JB_CUDA(c, dalloc(&c->d_tails, c->holes_cap));
+  }
+  StepParams P = make_params(c);
+  launch_compact(P, c->n, n_alive, c->d_holes, c->d_tails, c->d_counters + 4, c->stream);
+  c->launches += 2;
+  c->n = n_alive;
+  return JB_OK;
+}
+
+// SourcePhotons over local blocks [first, first + nb) (sourcing.cpp:25-205)
+static jb_status source_photons(jb_ctx *c, int first, int nb, int source_type, double t_start, double dt,
+                                int nblocks_npc, uint32_t call) {
+  if (c->cfg.source_strategy == JB_STRATEGY_ENERGY)
+    return fail(c, JB_ERR_UNSUPPORTED, "Energy source strategy not implemented!");
+  if (source_type == JB_SOURCE_EMISSION && !c->cfg.do_emission) return JB_OK;
+  if (nb <= 0) return JB_OK;
+  const int num_cells = c->mesh.nxb[0] * c->mesh.nxb[1] * c->mesh.nxb[2];
+  const double npc = static_cast<double>(c->cfg.num_particles) / num_cells / (nblocks_npc * c->mesh.nblocks);
+  const long long ncells = (long long)nb * num_cells;
+  StepParams P = make_params(c);
+  launch_source_count(P, first, nb, source_type, dt, npc, call, c->d_cnt, c->stream);
+  launch_exclusive_scan(c->d_cnt, c->d_prefix, ncells, c->d_scan, c->d_total, c->stream);
+  c->launches += 4;
+  JB_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_total, sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  const long long total = (long long)c->h_counters[0];
+  if (total < 0 || total > 0x7fffffffLL * (long long)nb) return fail(c, JB_ERR_CAPACITY, "photon count overflow");
+  if (c->n + total > c->capacity) {
+    if (c->requested_capacity > 0 && c->n + total > c->requested_capacity)
+      return fail(c, JB_ERR_CAPACITY, "photon pool capacity exceeded while sourcing (jb_set_capacity)");
+    jb_status s = ensure_capacity(c, c->n + total);
+    if (s != JB_OK) return s;
+    P = make_params(c);
+  }
+  launch_source_emit(P, first, nb, source_type, t_start, dt, call, c->d_prefix, c->n, c->stream);
+  c->launches += 1;
+  c->n += total;
+  JB_CUDA(c, cudaGetLastError());
+  return JB_OK;
+}
+
+static jb_status stats_begin(jb_ctx *c) {
+  memset(&c->stats, 0, sizeof(c->stats));
+  JB_CUDA(c, cudaMemsetAsync(c->d_stats, 0, sizeof(DStats), c->stream));
+  long long na = 0;
+  double e = 0.0;
+  jb_status s = census(c, 0.0, &na, nullptr, &e);
+  if (s != JB_OK) return s;
+  memset(c->h_stats, 0, sizeof(DStats));
+  c->stats.n_start = na;
+  c->stats.e_start = e;
+  return JB_OK;
+}
+static void fold_stats(jb_ctx *c) {
+  const DStats &h = *c->h_stats;
+  c->stats.n_sourced = (int64_t)h.n_sourced;
+  c->stats.n_absorbed = (int64_t)h.n_absorbed;
+  c->stats.n_escaped = (int64_t)h.n_escaped;
+  c->stats.n_sent = (int64_t)h.n_sent;
+  c->stats.n_received = (int64_t)h.n_received;
+  c->stats.n_block_crossings = (int64_t)h.n_crossings;
+  c->stats.n_segments = (int64_t)h.n_segments;
+  c->stats.n_scatters = (int64_t)h.n_scatters;
+  c->stats.n_ddmc_segments = (int64_t)h.n_ddmc;
+  c->stats.e_sourced = h.e_sourced;
+  c->stats.e_absorbed = h.e_absorbed;
+  c->stats.e_escaped = h.e_escaped;
+}
+static jb_status check_device_errors(jb_ctx *c) {
+  if (c->h_stats->n_error)
+    return fail(c, JB_ERR_STATE, "particle left the domain without a boundary condition");
+  if (c->h_stats->n_overflow)
+    return fail(c, JB_ERR_CAPACITY, "exchange outbox overflow: raise jb_set_capacity");
+  return JB_OK;
+}
+
+// all-to-all-v of the outboxes over NCCL: counts (all-gather) then grouped send/recv into
+// the inbox, then append to the pool. Returns the number of records sent by ALL ranks.
+static jb_status exchange_nccl(jb_ctx *c, double t_end, long long *global_sent) {
+  NcclApi &nc = nccl_api();
+  const int R = c->n_ranks;
+  if (!c->comm || !nc.ok) return fail(c, JB_ERR_COMM, "jb_comm_init has not been called");
+  if (!c->out.rec) {
+    jb_status s0 = ensure_capacity(c, std::max<long long>(c->capacity + 1, 1024));
+    if (s0 != JB_OK) return s0;
+  }
+#define JB_NCCL(call)                                                                                  \
+  do {                                                                                                 \
+    ncclResult_t r_ = (call);                                                                          \
+    if (r_ != ncclSuccess)                                                                             \
+      return fail(c, JB_ERR_COMM, std::string(#call) + ": " + (nc.GetErrorString ? nc.GetErrorString(r_) : "?")); \
+  } while (0)
+  JB_NCCL(nc.AllGather(c->out.count, c->d_count_matrix, (size_t)R, ncclUint64, c->comm, c->stream));
+  JB_CUDA(c, cudaMemcpyAsync(c->h_counters + 16, c->d_count_matrix, sizeof(unsigned long long) * R * R,
+                             cudaMemcpyDeviceToHost, c->stream));
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  const unsigned long long *M = c->h_counters + 16;  // M[src * R + dst]
+  long long total = 0, nrecv = 0;
+  for (int a = 0; a < R; ++a)
+    for (int b = 0; b < R; ++b) total += (long long)M[a * R + b];
+  for (int a = 0; a < R; ++a) nrecv += (long long)M[a * R + c->my_rank];
+  *global_sent = total;
+  if (total == 0) return JB_OK;
+  if (nrecv > c->inbox_cap) return fail(c, JB_ERR_CAPACITY, "exchange inbox overflow: raise jb_set_capacity");
+  if (c->n + nrecv > c->capacity) return fail(c, JB_ERR_CAPACITY, "photon pool capacity exceeded on receive");
+  JB_NCCL(nc.GroupStart());
+  long long roff = 0;
+  for (int peer = 0; peer < R; ++peer) {
+    const long long ns = (long long)M[c->my_rank * R + peer], nr = (long long)M[peer * R + c->my_rank];
+    if (ns > 0)
+      JB_NCCL(nc.Send(c->out.rec + (size_t)peer * c->out.cap, (size_t)ns * sizeof(ExRecord), ncclUint8, peer, c->comm,
+                      c->stream));
+    if (nr > 0) {
+      JB_NCCL(nc.Recv(c->d_inbox + roff, (size_t)nr * sizeof(ExRecord), ncclUint8, peer, c->comm, c->stream));
+      roff += nr;
+    }
+  }
+  JB_NCCL(nc.GroupEnd());
+#undef JB_NCCL
+  JB_CUDA(c, cudaMemsetAsync(c->out.count, 0, sizeof(unsigned long long) * R, c->stream));
+  if (nrecv > 0) {
+    StepParams P = make_params(c);
+    launch_unpack(P, c->d_inbox, nrecv, c->n, t_end, c->stream);
+    if (c->cfg.use_ddmc) launch_bface_range(P, c->n, nrecv, c->stream);
+    c->launches += 1 + (c->cfg.use_ddmc ? 1 : 0);
+    c->n += nrecv;
+  }
+  return JB_OK;
+}
+
+// sort the pool by (block, cell) with a counting sort; photons must be compacted. The
+// permutation is applied array by array through the one scratch array, whose storage
+// then swaps roles with the array just gathered.
+static jb_status sort_by_cell(jb_ctx *c) {
+  if (c->n <= 1) return JB_OK;
+  if (c->n > 0xffffffffLL) return fail(c, JB_ERR_CAPACITY, "sort supports < 2^32 photons per rank");
+  StepParams P = make_params(c);
+  cudaStream_t st = c->stream;
+  JB_CUDA(c, cudaMemsetAsync(c->d_cnt, 0, sizeof(int) * (size_t)c->ncells_local, st));
+  launch_sort_keys(P, c->n, c->d_cnt, st);
+  launch_exclusive_scan(c->d_cnt, c->d_prefix, c->ncells_local, c->d_scan, c->d_total, st);
+  launch_sort_perm(P, c->n, c->d_prefix, c->d_perm, st);
+  c->launches += 5;
+  void **arr[12];
+  swarm_arrays(c->s, arr);
+  for (auto pa : arr) {
+    launch_gather_b64(*pa, c->d_tmp, c->d_perm, c->n, st);
+    void *old = *pa;
+    *pa = (void *)c->d_tmp;
+    c->d_tmp = (double *)old;
+    c->launches++;
+  }
+  JB_CUDA(c, cudaGetLastError());
+  return JB_OK;
+}
+
+#define JB_REQUIRE_MESH(c)                                          \
+  do {                                                              \
+    if (!(c)) return JB_ERR_INVALID;                                \
+    if (!(c)->mesh_set) return fail((c), JB_ERR_STATE, "mesh not set"); \
+    JB_CUDA((c), cudaSetDevice((c)->device));                       \
+  } while (0)
+
+// ---- the individual tasks (jaybenne.hpp:59-69) -------------------------------------------
+jb_status jb_update_derived_transport_fields(jb_ctx *c, double dt) {
+  JB_REQUIRE_MESH(c);
+  StepParams P = make_params(c);
+  launch_fleck(P, dt, c->stream);
+  c->launches += 1;
+  if (c->cfg.use_ddmc) {
+    if ((int)c->local_gid.size() != c->mesh.nblocks)
+      return fail(c, JB_ERR_UNSUPPORTED, "DDMC face probabilities need every block on one rank (no ghost exchange yet)");
+    launch_face_prob(P, c->stream);
+    c->launches += c->mesh.ndim;
+  }
+  JB_CUDA(c, cudaGetLastError());
+  return JB_OK;
+}
+
+jb_status jb_source_photons(jb_ctx *c, int32_t source_type, double t_start, double dt) {
+  JB_REQUIRE_MESH(c);
+  const int nl = (int)c->local_gid.size();
+  const int nb = c->cfg.source_nblocks > 0 ? c->cfg.source_nblocks : nl;
+  jb_status s = source_photons(c, 0, nl, source_type, t_start, dt, nb, c->source_call);
+  if (s != JB_OK) return s;
+  if (!(source_type == JB_SOURCE_EMISSION && !c->cfg.do_emission)) c->source_call++;
+  return JB_OK;
+}
+
+jb_status jb_evaluate_radiation_energy(jb_ctx *c) {
+  JB_REQUIRE_MESH(c);
+  StepParams P = make_params(c);
+  launch_tally(P, c->n, c->stream);
+  c->launches += c->n > 0;
+  JB_CUDA(c, cudaGetLastError());
+  return JB_OK;
+}
+
+// InitializeRadiation on every local block (jaybenne.cpp:570-578). The reference sources
+// each block through its own MeshBlockData pack (nblocks = 1 in the per-cell count); the
+// blocks are independent, so one launch covers them all.
+jb_status jb_initialize_radiation(jb_ctx *c, int32_t is_thermal) {
+  JB_REQUIRE_MESH(c);
+  if (is_thermal) {
+    jb_status s = source_photons(c, 0, (int)c->local_gid.size(), JB_SOURCE_THERMAL, 0.0, 0.0, 1, c->source_call);
+    if (s != JB_OK) return s;
+    c->source_call++;
+  }
+  jb_status s = jb_evaluate_radiation_energy(c);
+  if (s != JB_OK) return s;
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return JB_OK;
+}
+
+// TransportPhotons / TransportPhotons_DDMC over the whole pool, then free the slots of the
+// photons that are gone (RemoveMarkedParticles, transport.cpp:176-178).
+static jb_status transport_range(jb_ctx *c, long long first, long long n, double t_start, double dt) {
+  StepParams P = make_params(c);
+  launch_transport(P, first, n, t_start, dt, c->stream);
+  c->launches += n > 0;
+  JB_CUDA(c, cudaGetLastError());
+  return JB_OK;
+}
+jb_status jb_transport_photons(jb_ctx *c, double t_start, double dt) {
+  JB_REQUIRE_MESH(c);
+  const unsigned long long dead0 = c->h_stats->n_dead;
+  jb_status s = transport_range(c, 0, c->n, t_start, dt);
+  if (s != JB_OK) return s;
+  s = sync_stats(c);
+  if (s != JB_OK) return s;
+  fold_stats(c);
+  s = check_device_errors(c);
+  if (s != JB_OK) return s;
+  return compact(c, (long long)(c->h_stats->n_dead - dead0));
+}
+
+jb_status jb_swarm_exchange(jb_ctx *c) {
+  JB_REQUIRE_MESH(c);
+  if (c->n_ranks == 1 || !c->comm) return JB_OK;  // on-rank hand-over happens inside the transport kernel
+  long long total = 0;
+  jb_status s = exchange_nccl(c, std::numeric_limits<double>::infinity(), &total);
+  if (s != JB_OK) return s;
+  return sync_stats(c);
+}
+
+jb_status jb_sample_ddmc_block_face(jb_ctx *c) {
+  JB_REQUIRE_MESH(c);
+  if (!c->cfg.use_ddmc) return JB_OK;
+  StepParams P = make_params(c);
+  launch_bface(P, c->n, c->stream);
+  c->launches += c->n > 0 && c->mesh.ndim > 1;
+  JB_CUDA(c, cudaGetLastError());
+  return JB_OK;
+}
+
+jb_status jb_check_completion(jb_ctx *c, double t_end, int64_t *num_unfinished) {
+  JB_REQUIRE_MESH(c);
+  long long u = 0;
+  jb_status s = census(c, t_end, nullptr, &u, nullptr);
+  if (num_unfinished) *num_unfinished = u;
+  return s;
+}
+
+jb_status jb_update_fluid(jb_ctx *c) {
+  JB_REQUIRE_MESH(c);
+  if (!c->cfg.do_feedback) return JB_OK;
+  StepParams P = make_params(c);
+  launch_update_fluid(P, c->stream);
+  c->launches += 1;
+  JB_CUDA(c, cudaGetLastError());
+  return JB_OK;
+}
+jb_status jb_update_derived_material(jb_ctx *c) {
+  JB_REQUIRE_MESH(c);
+  StepParams P = make_params(c);
+  launch_update_derived_material(P, c->stream);
+  c->launches += 1;
+  JB_CUDA(c, cudaGetLastError());
+  return JB_OK;
+}
+jb_status jb_post_initialization(jb_ctx *c) {
+  JB_REQUIRE_MESH(c);
+  StepParams P = make_params(c);
+  launch_post_initialization(P, c->stream);
+  c->launches += 1;
+  JB_CUDA(c, cudaGetLastError());
+  return JB_OK;
+}
+
+jb_status jb_stats_begin(jb_ctx *c) {
+  JB_REQUIRE_MESH(c);
+  return stats_begin(c);
+}
+
+jb_status jb_get_stats(jb_ctx *c, jb_cycle_stats *out) {
+  JB_REQUIRE_MESH(c);
+  if (!out) return JB_ERR_INVALID;
+  jb_status s = sync_stats(c);
+  if (s != JB_OK) return s;
+  fold_stats(c);
+  long long na = 0;
+  double e = 0.0;
+  s = census(c, 0.0, &na, nullptr, &e);
+  if (s != JB_OK) return s;
+  c->stats.n_end = na;
+  c->stats.e_end = e;
+  *out = c->stats;
+  return JB_OK;
+}
+
+// RadiationStep(...).Execute() (jaybenne.cpp:68-151)
+jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats *stats) {
+  JB_REQUIRE_MESH(c);
+  if (c->n_ranks > 1 && !c->comm)
+    return fail(c, JB_ERR_COMM, "multi-rank step needs jb_comm_init (or drive the tasks and jb_exchange_* from the host)");
+  cudaEventRecord(c->ev[0], c->stream);
+  jb_status s = stats_begin(c);
+  if (s != JB_OK) return s;
+  s = jb_update_derived_transport_fields(c, dt);
+  if (s != JB_OK) return s;
+  s = jb_source_photons(c, JB_SOURCE_EMISSION, t_start, dt);
+  if (s != JB_OK) return s;
+  bool done = false;
+  long long first = 0;
+  float ms_tr = 0.f;
+  for (int it = 1; it <= c->cfg.max_transport_iterations; ++it) {
+    c->stats.n_iterations = it;
+    cudaEventRecord(c->ev[2], c->stream);
+    s = transport_range(c, first, c->n - first, t_start, dt);
+    if (s != JB_OK) return s;
+    cudaEventRecord(c->ev[3], c->stream);
+    if (c->n_ranks == 1) {
+      s = sync_stats(c);
+      if (s != JB_OK) return s;
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]);
+      ms_tr += ms;
+      done = true;
+      break;
+    }
+    const long long n_before = c->n;
+    long long total_sent = 0;
+    s = exchange_nccl(c, t_start + dt, &total_sent);
+    if (s != JB_OK) return s;
+    {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]);
+      ms_tr += ms;
+    }
+    if (total_sent == 0) {
+      s = sync_stats(c);
+      if (s != JB_OK) return s;
+      done = true;
+      break;
+    }
+    first = n_before;  // only the arrivals still have t < t_end
+  }
+  fold_stats(c);
+  s = check_device_errors(c);
+  if (s != JB_OK) return s;
+  if (!done) return fail(c, JB_ERR_ITERATIONS, "max_transport_iterations exhausted");
+  s = compact(c, (long long)c->h_stats->n_dead);
+  if (s != JB_OK) return s;
+  s = jb_evaluate_radiation_energy(c);
+  if (s != JB_OK) return s;
+  s = jb_update_fluid(c);
+  if (s != JB_OK) return s;
+  if (c->cfg.sort_interval > 0 && (++c->cycles_since_sort) >= c->cfg.sort_interval) {
+    c->cycles_since_sort = 0;
+    s = sort_by_cell(c);
+    if (s != JB_OK) return s;
+  }
+  cudaEventRecord(c->ev[1], c->stream);
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  float ms_total = 0.f;
+  cudaEventElapsedTime(&ms_total, c->ev[0], c->ev[1]);
+  c->stats.ms_transport = ms_tr;
+  c->stats.ms_total = ms_total;
+  if (stats) {
+    long long na = 0;
+    double e = 0.0;
+    s = census(c, 0.0, &na, nullptr, &e);
+    if (s != JB_OK) return s;
+    c->stats.n_end = na;
+    c->stats.e_end = e;
+    *stats = c->stats;
+  }
+  return JB_OK;
+}
+
+// ---- swarm access ------------------------------------------------------------------------
+jb_status jb_num_particles(jb_ctx *c, int64_t *n_local) {
+  JB_REQUIRE_MESH(c);
+  if (n_local) *n_local = c->n;
+  return JB_OK;
+}
+
+jb_status jb_get_particles(jb_ctx *c, const jb_particles *d, int64_t capacity, int64_t *n_out) {
+  JB_REQUIRE_MESH(c);
+  if (!d || !n_out) return JB_ERR_INVALID;
+  const long long n = std::min<long long>(c->n, capacity);
+  *n_out = n;
+  if (n <= 0) return JB_OK;
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  struct { double *dst; const double *src; } f64[9] = {
+      {d->x, c->s.x}, {d->y, c->s.y}, {d->z, c->s.z}, {d->time, c->s.t}, {d->weight, c->s.w},
+      {d->energy, c->s.e}, {d->v0, c->s.vx}, {d->v1, c->s.vy}, {d->v2, c->s.vz}};
+  for (auto &a : f64)
+    if (a.dst) JB_CUDA(c, cudaMemcpy(a.dst, a.src, sizeof(double) * n, cudaMemcpyDeviceToHost));
+  if (d->i || d->j || d->k || d->block) {
+    std::vector<int2> loc((size_t)n);
+    JB_CUDA(c, cudaMemcpy(loc.data(), c->s.loc, sizeof(int2) * n, cudaMemcpyDeviceToHost));
+    const int n1 = c->mesh.nxb[0], n2 = c->mesh.nxb[1];
+    for (long long m = 0; m < n; ++m) {
+      const int cell = loc[m].y;
+      if (d->i) d->i[m] = cell % n1 + c->ng[0];
+      if (d->j) d->j[m] = (cell / n1) % n2 + c->ng[1];
+      if (d->k) d->k[m] = cell / (n1 * n2) + c->ng[2];
+      if (d->block) d->block[m] = loc[m].x >= 0 ? c->local_gid[loc[m].x] : -1;
+    }
+  }
+  if (d->rng) {
+    std::vector<uint2> a((size_t)n), b((size_t)n);
+    JB_CUDA(c, cudaMemcpy(a.data(), c->s.ida, sizeof(uint2) * n, cudaMemcpyDeviceToHost));
+    JB_CUDA(c, cudaMemcpy(b.data(), c->s.idb, sizeof(uint2) * n, cudaMemcpyDeviceToHost));
+    for (long long m = 0; m < n; ++m) {
+      d->rng[4 * m + 0] = a[m].x;
+      d->rng[4 * m + 1] = a[m].y;
+      d->rng[4 * m + 2] = b[m].x;
+      d->rng[4 * m + 3] = b[m].y;
+    }
+  }
+  return JB_OK;
+}
+
+jb_status jb_set_particles(jb_ctx *c, const jb_particles *s, int64_t n) {
+  JB_REQUIRE_MESH(c);
+  if (!s || n < 0) return JB_ERR_INVALID;
+  if (n > 0 && (!s->x || !s->time || !s->weight || !s->energy || !s->v0 || !s->v1 || !s->v2 || !s->block))
+    return fail(c, JB_ERR_INVALID, "x, time, weight, energy, v and block are required");
+  c->n = 0;
+  jb_status st = ensure_capacity(c, std::max<long long>(n, 1));
+  if (st != JB_OK) return st;
+  if (n == 0) return JB_OK;
+  std::vector<double> zeros;
+  auto up = [&](double *dst, const double *src) -> cudaError_t {
+    if (!src) {
+      zeros.assign((size_t)n, 0.0);
+      src = zeros.data();
+    }
+    return cudaMemcpy(dst, src, sizeof(double) * n, cudaMemcpyHostToDevice);
+  };
+  JB_CUDA(c, up(c->s.x, s->x)); JB_CUDA(c, up(c->s.y, s->y)); JB_CUDA(c, up(c->s.z, s->z));
+  JB_CUDA(c, up(c->s.t, s->time)); JB_CUDA(c, up(c->s.w, s->weight)); JB_CUDA(c, up(c->s.e, s->energy));
+  JB_CUDA(c, up(c->s.vx, s->v0)); JB_CUDA(c, up(c->s.vy, s->v1)); JB_CUDA(c, up(c->s.vz, s->v2));
+  std::vector<int2> loc((size_t)n);
+  std::vector<uint2> a((size_t)n), b((size_t)n);
+  for (long long m = 0; m < n; ++m) {
+    const int gid = s->block[m];
+    if (gid < 0 || gid >= c->mesh.nblocks || c->gid_to_local[gid] < 0) return fail(c, JB_ERR_INVALID, "block not local");
+    const jb_block &B = c->all_blocks[gid];
+    int ijk[3] = {0, 0, 0};
+    const double pos[3] = {s->x[m], s->y ? s->y[m] : 0.0, s->z ? s->z[m] : 0.0};
+    for (int d = 0; d < c->mesh.ndim; ++d) {
+      const double dxd = (B.xmax[d] - B.xmin[d]) / c->mesh.nxb[d];
+      ijk[d] = static_cast<int>(std::floor((pos[d] - B.xmin[d]) / dxd));
+    }
+    loc[m] = make_int2(c->gid_to_local[gid], (ijk[2] * c->mesh.nxb[1] + ijk[1]) * c->mesh.nxb[0] + ijk[0]);
+    a[m] = s->rng ? make_uint2(s->rng[4 * m], s->rng[4 * m + 1]) : make_uint2((uint32_t)m, (uint32_t)gid);
+    b[m] = s->rng ? make_uint2(s->rng[4 * m + 2], s->rng[4 * m + 3]) : make_uint2(0xffffffffu, 0u);
+  }
+  JB_CUDA(c, cudaMemcpy(c->s.loc, loc.data(), sizeof(int2) * n, cudaMemcpyHostToDevice));
+  JB_CUDA(c, cudaMemcpy(c->s.ida, a.data(), sizeof(uint2) * n, cudaMemcpyHostToDevice));
+  JB_CUDA(c, cudaMemcpy(c->s.idb, b.data(), sizeof(uint2) * n, cudaMemcpyHostToDevice));
+  c->n = n;
+  return JB_OK;
+}
+
+// ---- event log ---------------------------------------------------------------------------
+jb_status jb_event_log_enable(jb_ctx *c, int64_t capacity) {
+  if (!c) return JB_ERR_INVALID;
+  JB_CUDA(c, cudaSetDevice(c->device));
+  dfree(c->d_events);
+  c->d_events = nullptr;
+  c->event_cap = 0;
+  if (capacity > 0) {
+    JB_CUDA(c, dalloc(&c->d_events, capacity));
+    c->event_cap = capacity;
+  }
+  JB_CUDA(c, cudaMemset(&c->d_stats->n_events, 0, sizeof(unsigned long long)));
+  return JB_OK;
+}
+jb_status jb_event_log_read(jb_ctx *c, jb_event *dst, int64_t capacity, int64_t *n) {
+  if (!c || !n) return JB_ERR_INVALID;
+  JB_CUDA(c, cudaSetDevice(c->device));
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  unsigned long long cnt = 0;
+  JB_CUDA(c, cudaMemcpy(&cnt, &c->d_stats->n_events, sizeof(cnt), cudaMemcpyDeviceToHost));
+  *n = (int64_t)cnt;
+  const long long m = std::min<long long>(std::min<long long>(capacity, (long long)cnt), c->event_cap);
+  if (m > 0 && dst) JB_CUDA(c, cudaMemcpy(dst, c->d_events, sizeof(jb_event) * m, cudaMemcpyDeviceToHost));
+  return JB_OK;
+}
+
+// ---- exchange, host-driven flavours ------------------------------------------------------
+int64_t jb_exchange_record_bytes(void) { return (int64_t)sizeof(ExRecord); }
+
+static jb_status outbox_counts(jb_ctx *c) {
+  JB_CUDA(c, cudaMemcpyAsync(c->h_counters + 8, c->out.count, sizeof(unsigned long long) * c->n_ranks,
+                             cudaMemcpyDeviceToHost, c->stream));
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return JB_OK;
+}
+jb_status jb_exchange_count(jb_ctx *c, int32_t peer, int64_t *n_records) {
+  JB_REQUIRE_MESH(c);
+  if (peer < 0 || peer >= c->n_ranks || !n_records) return JB_ERR_INVALID;
+  *n_records = 0;
+  if (!c->out.count) return JB_OK;
+  jb_status s = outbox_counts(c);
+  if (s != JB_OK) return s;
+  *n_records = (int64_t)c->h_counters[8 + peer];
+  return JB_OK;
+}
+jb_status jb_exchange_take_device(jb_ctx *c, int32_t peer, void **dev_ptr, int64_t *n_records) {
+  JB_REQUIRE_MESH(c);
+  if (peer < 0 || peer >= c->n_ranks || !n_records || !dev_ptr) return JB_ERR_INVALID;
+  *n_records = 0;
+  *dev_ptr = nullptr;
+  if (!c->out.count || !c->out.rec) return JB_OK;
+  jb_status s = outbox_counts(c);
+  if (s != JB_OK) return s;
+  *n_records = (int64_t)c->h_counters[8 + peer];
+  *dev_ptr = c->out.rec + (size_t)peer * c->out.cap;
+  JB_CUDA(c, cudaMemsetAsync(c->out.count + peer, 0, sizeof(unsigned long long), c->stream));
+  return JB_OK;
+}
+jb_status jb_exchange_take(jb_ctx *c, int32_t peer, void *dst, int64_t capacity, int64_t *n_records) {
+  void *p = nullptr;
+  int64_t n = 0;
+  if (!c || !n_records) return JB_ERR_INVALID;
+  if (peer < 0 || peer >= c->n_ranks) return JB_ERR_INVALID;
+  // look before taking so a short buffer does not lose the records
+  jb_status s = jb_exchange_count(c, peer, &n);
+  if (s != JB_OK) return s;
+  if (n > capacity) return fail(c, JB_ERR_CAPACITY, "exchange buffer too small");
+  s = jb_exchange_take_device(c, peer, &p, &n);
+  if (s != JB_OK) return s;
+  if (n > 0) JB_CUDA(c, cudaMemcpy(dst, p, sizeof(ExRecord) * n, cudaMemcpyDeviceToHost));
+  *n_records = n;
+  return JB_OK;
+}
+jb_status jb_exchange_give_device(jb_ctx *c, const void *dev_ptr, int64_t n_records) {
+  JB_REQUIRE_MESH(c);
+  if (n_records <= 0) return JB_OK;
+  if (c->n + n_records > c->capacity) {
+    if (c->requested_capacity > 0 && c->n + n_records > c->requested_capacity)
+      return fail(c, JB_ERR_CAPACITY, "photon pool capacity exceeded on receive");
+    jb_status s = ensure_capacity(c, c->n + n_records);
+    if (s != JB_OK) return s;
+  }
+  StepParams P = make_params(c);
+  launch_unpack(P, (const ExRecord *)dev_ptr, n_records, c->n, std::numeric_limits<double>::infinity(), c->stream);
+  c->launches += 1;
+  c->n += n_records;
+  jb_status s = sync_stats(c);
+  if (s != JB_OK) return s;
+  fold_stats(c);
+  if (c->h_stats->n_error) return fail(c, JB_ERR_COMM, "record for a block that is not local");
+  return JB_OK;
+}
+jb_status jb_exchange_give(jb_ctx *c, const void *src_host, int64_t n_records) {
+  JB_REQUIRE_MESH(c);
+  if (n_records <= 0) return JB_OK;
+  ExRecord *stage = nullptr;
+  JB_CUDA(c, dalloc(&stage, n_records));
+  cudaError_t e = cudaMemcpy(stage, src_host, sizeof(ExRecord) * n_records, cudaMemcpyHostToDevice);
+  jb_status s = e == cudaSuccess ? jb_exchange_give_device(c, stage, n_records)
+                                 : fail(c, JB_ERR_CUDA, cudaGetErrorString(e));
+  cudaStreamSynchronize(c->stream);
+  cudaFree(stage);
+  return s;
+}
+jb_status jb_exchange_clear(jb_ctx *c) {
+  JB_REQUIRE_MESH(c);
+  if (c->out.count) JB_CUDA(c, cudaMemsetAsync(c->out.count, 0, sizeof(unsigned long long) * c->n_ranks, c->stream));
+  return JB_OK;
+}
+
+// ---- NCCL communicator -------------------------------------------------------------------
+jb_status jb_comm_unique_id(void *id128) {
+  if (!id128) return JB_ERR_INVALID;
+  NcclApi &nc = nccl_api();
+  if (!nc.ok) return JB_ERR_COMM;
+  ncclUniqueId id;
+  if (nc.GetUniqueId(&id) != ncclSuccess) return JB_ERR_COMM;
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  memcpy(id128, &id, 128);
+  return JB_OK;
+}
+jb_status jb_comm_init(jb_ctx *c, const void *id128, int32_t rank, int32_t n_ranks) {
+  if (!c || !id128) return JB_ERR_INVALID;
+  NcclApi &nc = nccl_api();
+  if (!nc.ok) return fail(c, JB_ERR_COMM, "libnccl.so.2 could not be loaded");
+  if (c->mesh_set && (rank != c->my_rank || n_ranks != c->n_ranks))
+    return fail(c, JB_ERR_INVALID, "rank / n_ranks differ from jb_set_mesh");
+  JB_CUDA(c, cudaSetDevice(c->device));
+  ncclUniqueId id;
+  memcpy(&id, id128, 128);
+  ncclResult_t r = nc.CommInitRank(&c->comm, n_ranks, id, rank);
+  if (r != ncclSuccess) return fail(c, JB_ERR_COMM, std::string("ncclCommInitRank: ") + (nc.GetErrorString ? nc.GetErrorString(r) : "?"));
+  return JB_OK;
+}
+
+// kernels launched by this context so far (bench.py reports it as gpu_launches)
+int64_t jb_kernel_launches(const jb_ctx *c) { return c ? c->launches : 0; }
+
+}  // extern "C"
