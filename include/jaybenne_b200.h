@@ -243,6 +243,10 @@ jb_status jb_get_stats(jb_ctx *ctx, jb_cycle_stats *stats);
 /* zero the counters and record n_start / e_start: for hosts that drive the individual
  * tasks themselves (jb_radiation_step does this internally) */
 jb_status jb_stats_begin(jb_ctx *ctx);
+/* device timer: CUDA events recorded on the library's stream (all kernels of a context
+ * run on one private stream); stop waits for the stream and returns the elapsed ms */
+jb_status jb_timer_start(jb_ctx *ctx);
+jb_status jb_timer_stop(jb_ctx *ctx, double *ms);
 /* CUDA kernels launched by this context since jb_create (diagnostics / bench.py) */
 int64_t jb_kernel_launches(const jb_ctx *ctx);
 

@@ -150,6 +150,8 @@ DEVICE_API = {
     "config_default": (None, [C.POINTER(jb_config)]),
     "abi_version": (C.c_int, []),
     "kernel_launches": (C.c_int64, [ctx_p]),
+    "timer_start": (C.c_int, [ctx_p]),
+    "timer_stop": (C.c_int, [ctx_p, _pd]),
     "comm_unique_id": (C.c_int, [C.c_void_p]),
     "comm_init": (C.c_int, [ctx_p, C.c_void_p, C.c_int32, C.c_int32]),
     "exchange_take_device": (C.c_int, [ctx_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),

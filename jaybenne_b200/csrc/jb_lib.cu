@@ -64,6 +64,7 @@ struct jb_ctx {
   int device = -1;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t tev[2] = {nullptr, nullptr};
 
   // device tables
   DBlock *d_blocks = nullptr;
@@ -257,8 +258,6 @@ static jb_status ensure_capacity(jb_ctx *c, long long need) {
   c->s = ns;
   c->n = keep_n;
   c->capacity = cap;
-  JB_CUDA(c, dalloc(&c->d_tmp, cap));
-  JB_CUDA(c, dalloc(&c->d_perm, cap));
   if (c->n_ranks > 1) {
     c->out.cap = std::max<long long>(cap / (2 * c->n_ranks), 4096);
     JB_CUDA(c, dalloc(&c->out.rec, c->out.cap * c->n_ranks));
@@ -325,6 +324,8 @@ void jb_destroy(jb_ctx *c) {
   if (c->h_stats) cudaFreeHost(c->h_stats);
   if (c->h_counters) cudaFreeHost(c->h_counters);
   for (auto &e : c->ev)
+    if (e) cudaEventDestroy(e);
+  for (auto &e : c->tev)
     if (e) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
@@ -661,6 +662,10 @@ static jb_status exchange_nccl(jb_ctx *c, double t_end, long long *global_sent) 
 static jb_status sort_by_cell(jb_ctx *c) {
   if (c->n <= 1) return JB_OK;
   if (c->n > 0xffffffffLL) return fail(c, JB_ERR_CAPACITY, "sort supports < 2^32 photons per rank");
+  if (!c->d_tmp) {  // sort scratch is only allocated when sorting is used
+    JB_CUDA(c, dalloc(&c->d_tmp, c->capacity));
+    JB_CUDA(c, dalloc(&c->d_perm, c->capacity));
+  }
   StepParams P = make_params(c);
   cudaStream_t st = c->stream;
   JB_CUDA(c, cudaMemsetAsync(c->d_cnt, 0, sizeof(int) * (size_t)c->ncells_local, st));
@@ -962,7 +967,11 @@ jb_status jb_get_particles(jb_ctx *c, const jb_particles *d, int64_t capacity, i
 
 jb_status jb_set_particles(jb_ctx *c, const jb_particles *s, int64_t n) {
   JB_REQUIRE_MESH(c);
-  if (!s || n < 0) return JB_ERR_INVALID;
+  if (n < 0 || (n > 0 && !s)) return JB_ERR_INVALID;
+  if (n == 0) {
+    c->n = 0;
+    return JB_OK;
+  }
   if (n > 0 && (!s->x || !s->time || !s->weight || !s->energy || !s->v0 || !s->v1 || !s->v2 || !s->block))
     return fail(c, JB_ERR_INVALID, "x, time, weight, energy, v and block are required");
   c->n = 0;
@@ -1135,6 +1144,28 @@ jb_status jb_comm_init(jb_ctx *c, const void *id128, int32_t rank, int32_t n_ran
   memcpy(&id, id128, 128);
   ncclResult_t r = nc.CommInitRank(&c->comm, n_ranks, id, rank);
   if (r != ncclSuccess) return fail(c, JB_ERR_COMM, std::string("ncclCommInitRank: ") + (nc.GetErrorString ? nc.GetErrorString(r) : "?"));
+  return JB_OK;
+}
+
+// CUDA-event timer on the library's own stream (torch.cuda.Event only sees torch's stream)
+jb_status jb_timer_start(jb_ctx *c) {
+  if (!c) return JB_ERR_INVALID;
+  JB_CUDA(c, cudaSetDevice(c->device));
+  if (!c->tev[0]) {
+    JB_CUDA(c, cudaEventCreate(&c->tev[0]));
+    JB_CUDA(c, cudaEventCreate(&c->tev[1]));
+  }
+  JB_CUDA(c, cudaEventRecord(c->tev[0], c->stream));
+  return JB_OK;
+}
+jb_status jb_timer_stop(jb_ctx *c, double *ms) {
+  if (!c || !ms || !c->tev[0]) return JB_ERR_INVALID;
+  JB_CUDA(c, cudaSetDevice(c->device));
+  JB_CUDA(c, cudaEventRecord(c->tev[1], c->stream));
+  JB_CUDA(c, cudaEventSynchronize(c->tev[1]));
+  float f = 0.f;
+  JB_CUDA(c, cudaEventElapsedTime(&f, c->tev[0], c->tev[1]));
+  *ms = f;
   return JB_OK;
 }
 

@@ -229,6 +229,17 @@ class Jaybenne:
     def kernel_launches(self) -> int:
         return int(self.api.kernel_launches(self._ctx))
 
+    def timer_start(self):
+        self._check(self.api.timer_start(self._ctx))
+
+    def timer_stop(self) -> float:
+        ms = C.c_double()
+        self._check(self.api.timer_stop(self._ctx, C.byref(ms)))
+        return ms.value
+
+    def clear_particles(self):
+        self._check(self.api.set_particles(self._ctx, None, 0))
+
     def comm_init(self, unique_id: bytes):
         self._check(self.api.comm_init(self._ctx, unique_id, self.rank, self.n_ranks))
 

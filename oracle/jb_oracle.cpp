@@ -1011,9 +1011,25 @@ static jb_status source_photons(Ctx *c, const std::vector<int> &which, int sourc
       update += static_cast<int>(std::round(b.src_num[idx]));
     }
   }
-  // pass 2 (SourcePhotons2)
+  // pass 2 (SourcePhotons2). The new photons of cell ci occupy pool slots base + prefix[ci]..,
+  // i.e. the order a serial push_back would give, so timing builds can run cells in parallel.
   for (size_t w = 0; w < which.size(); ++w) {
     Block &b = c->blocks[which[w]];
+    const size_t base = b.pool.size();
+    {
+      const int last = num_cells - 1;
+      const size_t nnew = (size_t)prefix[w][last] + (size_t)static_cast<int>(std::round(b.src_num[last]));
+      Particle blank;
+      memset(&blank, 0, sizeof(blank));
+      b.pool.resize(base + nnew, blank);
+    }
+    long long r_n = 0;
+    double r_e = 0.0;
+    const bool serial = c->cfg.rng_mode == JB_RNG_XORSHIFT_POOL;
+    (void)serial;
+#if defined(_OPENMP)
+#pragma omp parallel for collapse(3) schedule(static) reduction(+ : r_n, r_e) if (!serial)
+#endif
     for (int k = 0; k < nx3; ++k)
       for (int j = 0; j < nx2; ++j)
         for (int i = 0; i < nx1; ++i) {
@@ -1054,11 +1070,13 @@ static jb_status source_photons(Ctx *c, const std::vector<int> &which, int sourc
               p.t = 0.;
             }
             p.rn = rng.n;
-            b.pool.push_back(p);
-            c->stats.n_sourced++;
-            c->stats.e_sourced += p.w;
+            b.pool[base + (size_t)np] = p;
+            r_n++;
+            r_e += p.w;
           }
         }
+    c->stats.n_sourced += r_n;
+    c->stats.e_sourced += r_e;
   }
   c->source_call++;
   return JB_OK;
@@ -1081,7 +1099,19 @@ static jb_status transport_photons(Ctx *c, double t_start, double dt) {
   for (Block &b : c->blocks) {
     const double dx_i = b.dx[0], dx_j = b.dx[1], dx_k = b.dx[2];
     const double dx_push = std::min(dx_i, std::min(dx_j, dx_k));
-    for (Particle &p : b.pool) {
+    // Timing builds (-fopenmp) spread the photons of a block over the host threads, like the
+    // reference's Kokkos OpenMP backend does; counters become reductions and the tally an
+    // atomic add. Parity builds are compiled without OpenMP and run this loop serially.
+    long long r_seg = 0, r_ddmc = 0, r_abs = 0, r_scat = 0;
+    double r_eabs = 0.0;
+    const long long npool = (long long)b.pool.size();
+    const bool serial = c->log_events || c->cfg.rng_mode == JB_RNG_XORSHIFT_POOL;
+    (void)serial;
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(dynamic, 1024) reduction(+ : r_seg, r_ddmc, r_abs, r_scat, r_eabs) if (!serial)
+#endif
+    for (long long pi = 0; pi < npool; ++pi) {
+      Particle &p = b.pool[pi];
       RngGen rng = particle_rng(c, p);
       double &t = p.t, &vx = p.vx, &vy = p.vy, &vz = p.vz;
       const double ww = p.w, ee = p.e;
@@ -1090,7 +1120,7 @@ static jb_status transport_photons(Ctx *c, double t_start, double dt) {
       Xtoijk(c, b, x, y, z, ip, jp, kp);
       while (t < t_start + dt) {
         const uint32_t draw0 = rng.n;
-        c->stats.n_segments++;
+        r_seg++;
         double xl = Xc(c, b, 0, ip) - 0.5 * dx_i, xu = Xc(c, b, 0, ip) + 0.5 * dx_i;
         double yl = Xc(c, b, 1, jp) - 0.5 * dx_j, yu = Xc(c, b, 1, jp) + 0.5 * dx_j;
         double zl = Xc(c, b, 2, kp) - 0.5 * dx_k, zu = Xc(c, b, 2, kp) + 0.5 * dx_k;
@@ -1103,7 +1133,7 @@ static jb_status transport_photons(Ctx *c, double t_start, double dt) {
         bool is_absorbed = false, is_scattered = false, is_rejected = false;
         const bool is_ddmc_step = use_ddmc && (dx_push * (ss + aa) > tau_ddmc);
         if (is_ddmc_step) {
-          c->stats.n_ddmc_segments++;
+          r_ddmc++;
           Xtoijk(c, b, x, y, z, ip, jp, kp);
           xl = Xc(c, b, 0, ip) - 0.5 * dx_i, xu = Xc(c, b, 0, ip) + 0.5 * dx_i;
           yl = Xc(c, b, 1, jp) - 0.5 * dx_j, yu = Xc(c, b, 1, jp) + 0.5 * dx_j;
@@ -1140,10 +1170,14 @@ static jb_status transport_photons(Ctx *c, double t_start, double dt) {
           break;
         }
         if (is_absorbed) {
-          b.edelta[cidx(c, kp, jp, ip)] += ww;
+          double &dejbn = b.edelta[cidx(c, kp, jp, ip)];
+#if defined(_OPENMP)
+#pragma omp atomic
+#endif
+          dejbn += ww;
           p.marked = true;
-          c->stats.n_absorbed++;
-          c->stats.e_absorbed += ww;
+          r_abs++;
+          r_eabs += ww;
           if (c->log_events) {
             const double v[3] = {vx, vy, vz};
             log_event(c, p, draw0, kind | JB_EV_ABSORB, b.info.gid, v);
@@ -1152,7 +1186,7 @@ static jb_status transport_photons(Ctx *c, double t_start, double dt) {
         }
         if (is_scattered) {
           scatter_iso(rng, vv, vx, vy, vz);
-          c->stats.n_scatters++;
+          r_scat++;
           kind |= JB_EV_SCATTER;
         }
         if (c->log_events) {
@@ -1162,6 +1196,11 @@ static jb_status transport_photons(Ctx *c, double t_start, double dt) {
       }
       p.rn = rng.n;
     }
+    c->stats.n_segments += r_seg;
+    c->stats.n_ddmc_segments += r_ddmc;
+    c->stats.n_absorbed += r_abs;
+    c->stats.n_scatters += r_scat;
+    c->stats.e_absorbed += r_eabs;
     remove_marked(b);
   }
   return JB_OK;
