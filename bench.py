@@ -238,7 +238,9 @@ def main():
     nblocks_total = (cells // nb) ** 3
     over = {"source_nblocks": nblocks_total, "sort_interval": args.sort_interval,
             "gray_mode": capi.JB_GRAY_DIRECT if args.gray_direct else capi.JB_GRAY_KIRCHHOFF}
-    cap = int(particles / world * (1.03 if world == 1 else 1.25)) + 200000
+    # thermal photons + one cycle's emission (particles / nblocks_total, sourcing.cpp:68-69) + slack for the
+    # uneven spread of photons over ranks
+    cap = int(particles * (1.0 + 1.0 / nblocks_total) / world * (1.02 if world == 1 else 1.25)) + 200000
     mb = Mcblock(pin, rank=rank, n_ranks=world, capacity=cap, cfg_overrides=over)
     jb = mb.jb
     if world > 1:
