@@ -138,6 +138,34 @@ __device__ __forceinline__ double absorption_coeff(const Closure &cl, double rho
   return alpha * cl.length_unit;
 }
 
+// The same closure with the factors that depend on the photon alone taken out of the segment
+// loop: h*nu and 2 h nu^3 / c^2 are evaluated once per photon by exactly the operations
+// planck_bnu() would perform (association included), so the value is bit-identical.
+struct PhotonFreq {
+  double f, hnu, bpref;  // nu in CGS, h*nu, (2*h*nu*nu*nu/(c*c)) * 1.
+};
+__device__ __forceinline__ PhotonFreq photon_freq(const Closure &cl, double nu) {
+  PhotonFreq q;
+  q.f = nu * cl.freq_unit;
+  q.hnu = cl.h * q.f;
+  q.bpref = (2. * cl.h * q.f * q.f * q.f / (cl.c * cl.c)) * 1.;
+  return q;
+}
+__device__ __forceinline__ double absorption_coeff_hoisted(const Closure &cl, double rho, double temp,
+                                                           const PhotonFreq &q) {
+  const double r = cl.rho_unit * rho, T = cl.temp_unit * temp;
+  double alpha;
+  if (cl.opacity_model == JB_OPAC_GRAY && cl.gray_mode == JB_GRAY_DIRECT) {
+    alpha = r * cl.kappa;
+  } else {
+    const double x = q.hnu / (cl.kb * T);
+    const double Bnu = q.bpref / jbm::expm1(x);
+    const double jnu = cl.opacity_model == JB_OPAC_GRAY ? r * cl.kappa * Bnu : epbremss_jnu(cl, r, T, q.f);
+    alpha = robust_ratio(jnu, Bnu);
+  }
+  return alpha * cl.length_unit;
+}
+
 // Scattering::TotalScatteringCoefficient (NonCGSUnitsS<GrayS|ThomsonS>)
 __device__ __forceinline__ double scattering_coeff(const Closure &cl, double rho) {
   const double r = cl.rho_unit * rho;
@@ -229,9 +257,13 @@ __device__ __forceinline__ double planck_energy(const Closure &cl, Rng &rng, con
 // One IMC segment (ptcl_transport_step, transport_utils.hpp:111-160): distances to
 // effective absorption / effective scatter / census / cell faces, capped at the smallest
 // cell width; advance; nudge across a face the photon has reached.
+// di/dj/dk report which face nudge fired (-1 lower, +1 upper, 0 none): after a nudge the
+// photon sits eps_imc_offset cell widths beyond that face, every other end point is at least
+// that far inside, so the cell index moves by exactly that amount (see k_transport_imc).
 template <int NDIM>
-__device__ __forceinline__ void imc_step(Rng &rng, const double t_end, const CellEnv &c, const double vv,
-                                         const double dx_cell, Photon &p, bool &is_absorbed, bool &is_scattered) {
+__device__ __forceinline__ void imc_step_idx(Rng &rng, const double t_end, const CellEnv &c, const double vv,
+                                             const double dx_cell, Photon &p, bool &is_absorbed, bool &is_scattered,
+                                             int &di, int &dj, int &dk) {
   constexpr bool multi_d = NDIM >= 2, three_d = NDIM == 3;
   const double rmin = DBL_MIN;
   const double lam_abs = 1.0 / (c.ff * c.aa + rmin);
@@ -269,12 +301,27 @@ __device__ __forceinline__ void imc_step(Rng &rng, const double t_end, const Cel
   const double fdx = EPS_IMC * (c.xu - c.xl);
   const double fdy = EPS_IMC * (c.yu - c.yl);
   const double fdz = EPS_IMC * (c.zu - c.zl);
-  p.x = (fabs(p.x - c.xl) < fdx) ? c.xl - fdx : p.x;
-  p.x = (fabs(p.x - c.xu) < fdx) ? c.xu + fdx : p.x;
-  p.y = (multi_d && fabs(p.y - c.yl) < fdy) ? c.yl - fdy : p.y;
-  p.y = (multi_d && fabs(p.y - c.yu) < fdy) ? c.yu + fdy : p.y;
-  p.z = (three_d && fabs(p.z - c.zl) < fdz) ? c.zl - fdz : p.z;
-  p.z = (three_d && fabs(p.z - c.zu) < fdz) ? c.zu + fdz : p.z;
+  const bool nxl = fabs(p.x - c.xl) < fdx;
+  p.x = nxl ? c.xl - fdx : p.x;
+  const bool nxu = fabs(p.x - c.xu) < fdx;
+  p.x = nxu ? c.xu + fdx : p.x;
+  const bool nyl = multi_d && fabs(p.y - c.yl) < fdy;
+  p.y = nyl ? c.yl - fdy : p.y;
+  const bool nyu = multi_d && fabs(p.y - c.yu) < fdy;
+  p.y = nyu ? c.yu + fdy : p.y;
+  const bool nzl = three_d && fabs(p.z - c.zl) < fdz;
+  p.z = nzl ? c.zl - fdz : p.z;
+  const bool nzu = three_d && fabs(p.z - c.zu) < fdz;
+  p.z = nzu ? c.zu + fdz : p.z;
+  di = nxu ? 1 : (nxl ? -1 : 0);
+  dj = nyu ? 1 : (nyl ? -1 : 0);
+  dk = nzu ? 1 : (nzl ? -1 : 0);
+}
+template <int NDIM>
+__device__ __forceinline__ void imc_step(Rng &rng, const double t_end, const CellEnv &c, const double vv,
+                                         const double dx_cell, Photon &p, bool &is_absorbed, bool &is_scattered) {
+  int di, dj, dk;
+  imc_step_idx<NDIM>(rng, t_end, c, vv, dx_cell, p, is_absorbed, is_scattered, di, dj, dk);
 }
 
 __device__ __forceinline__ bool fuzzy_eq(const double a, const double b, const double c, const double eps) {

@@ -37,6 +37,28 @@ __device__ __forceinline__ void warp_add_f64(double *dst, double v) {
   v = warp_sum_f64(v);
   if ((threadIdx.x & 31) == 0 && v != 0.0) atomicAdd(dst, v);
 }
+// energy sums: warp tree, then one add into the bin of this warp (see EBINS in jb_kernels.cuh)
+__device__ __forceinline__ void warp_add_energy(const StepParams &P, int kind, double v) {
+  v = warp_sum_f64(v);
+  if ((threadIdx.x & 31) == 0 && v != 0.0) {
+    const unsigned gw = (unsigned)((blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x) >> 5);
+    atomicAdd(&P.ebins[kind * EBINS + (gw & (EBINS - 1))], v);
+  }
+}
+// pairwise fold of one kind's bins: *dst = sum(bins)
+__global__ void k_fold_bins(const double *bins, double *dst) {
+  __shared__ double sh[EBINS];
+  sh[threadIdx.x] = bins[threadIdx.x];
+  __syncthreads();
+  for (int o = EBINS / 2; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *dst = sh[0];
+}
+void launch_fold_bins(const StepParams &P, int kind, double *dst, cudaStream_t st) {
+  k_fold_bins<<<1, EBINS, 0, st>>>(P.ebins + kind * EBINS, dst);
+}
 
 // UniformCartesian::Xc<dir>(idx), idx given as interior index
 __device__ __forceinline__ double cell_center(const DBlock &b, const int ng, const int d, const int i) {
@@ -88,6 +110,19 @@ __global__ void k_fleck(StepParams P, double dt, long long ncells) {
     const double cv = P.cl.cv;
     const double emis = emissivity(P.cl, rho, temp);
     P.f.fleck[c] = 1.0 / (1.0 + (4.0 * emis / (rho * cv * temp)) * dt);
+  }
+}
+
+// per-cell lookup record of the IMC segment loop (CellProps)
+__global__ void k_pack_props(StepParams P, long long ncells) {
+  for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncells;
+       c += (long long)gridDim.x * blockDim.x) {
+    CellProps cp;
+    cp.rho = P.f.rho[c];
+    cp.temp = eos_temperature(P.cl, P.f.sie[c]);
+    cp.ff = P.f.fleck[c];
+    cp.ss = scattering_coeff(P.cl, cp.rho);
+    P.f.props[c] = cp;
   }
 }
 
@@ -401,7 +436,7 @@ __global__ void k_source_emit(StepParams P, int first_local, long long ncells, i
     }
   }
   warp_add_u64(&P.stats->n_sourced, my_n);
-  warp_add_f64(&P.stats->e_sourced, my_e);
+  warp_add_energy(P, EB_SOURCED, my_e);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -758,7 +793,7 @@ __global__ void __launch_bounds__(128) k_transport(StepParams P, long long first
   warp_add_u64(&S->n_crossings, c_cross);
   warp_add_u64(&S->n_absorbed, c_abs);
   warp_add_u64(&S->n_dead, c_abs + c_esc + c_sent + c_err + c_ovf);
-  warp_add_f64(&S->e_absorbed, e_abs);
+  warp_add_energy(P, EB_ABSORBED, e_abs);
   if (DDMC) warp_add_u64(&S->n_ddmc, c_ddmc);
   // rare channels: skip the shuffles unless some lane has something
   if (__any_sync(0xffffffffu, (c_esc | c_sent | c_err | c_ovf) != 0)) {
@@ -766,7 +801,7 @@ __global__ void __launch_bounds__(128) k_transport(StepParams P, long long first
     warp_add_u64(&S->n_sent, c_sent);
     warp_add_u64(&S->n_error, c_err);
     warp_add_u64(&S->n_overflow, c_ovf);
-    warp_add_f64(&S->e_escaped, e_esc);
+    warp_add_energy(P, EB_ESCAPED, e_esc);
   }
 }
 
@@ -783,10 +818,20 @@ static void launch_transport_nd(const StepParams &P, long long first, long long 
     k_transport<NDIM, DDMC, false><<<(unsigned)blocks, threads, 0, st>>>(P, first, n, t_start, dt);
 }
 
+#include "jb_transport_imc.cuh"
+
 void launch_transport(const StepParams &P, long long first, long long n, double t_start, double dt,
                       cudaStream_t st) {
   if (n <= 0) return;
   const bool dd = P.use_ddmc != 0;
+  if (!dd && P.log.cap <= 0 && g_tuning.variant == 1) {
+    switch (P.mesh.ndim) {
+      case 1: launch_transport_imc<1>(P, first, n, t_start, dt, st); break;
+      case 2: launch_transport_imc<2>(P, first, n, t_start, dt, st); break;
+      default: launch_transport_imc<3>(P, first, n, t_start, dt, st); break;
+    }
+    return;
+  }
   switch (P.mesh.ndim) {
     case 1: dd ? launch_transport_nd<1, true>(P, first, n, t_start, dt, st) : launch_transport_nd<1, false>(P, first, n, t_start, dt, st); break;
     case 2: dd ? launch_transport_nd<2, true>(P, first, n, t_start, dt, st) : launch_transport_nd<2, false>(P, first, n, t_start, dt, st); break;
@@ -844,6 +889,10 @@ void launch_fleck(const StepParams &P, double dt, cudaStream_t st) {
   const long long ncells = (long long)P.mesh.nlocal * P.mesh.ncell;
   if (ncells <= 0) return;
   k_fleck<<<grid_for(ncells, 256), 256, 0, st>>>(P, dt, ncells);
+}
+void launch_pack_props(const StepParams &P, cudaStream_t st) {
+  const long long ncells = (long long)P.mesh.nlocal * P.mesh.ncell;
+  if (ncells > 0) k_pack_props<<<grid_for(ncells, 256), 256, 0, st>>>(P, ncells);
 }
 void launch_face_prob(const StepParams &P, cudaStream_t st) {
   for (int d = 0; d < P.mesh.ndim; ++d) {
@@ -924,7 +973,7 @@ void launch_post_initialization(const StepParams &P, cudaStream_t st) {
 // CheckCompletion (transport.cpp:198-209) + census sums: photons in use, photons with
 // t < t_end, and the energy they carry.
 __global__ void k_census(StepParams P, long long n, double t_end, unsigned long long *n_alive,
-                         unsigned long long *n_unfinished, double *e_sum) {
+                         unsigned long long *n_unfinished) {
   unsigned long long a = 0, u = 0;
   double e = 0.0;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < n;
@@ -936,11 +985,13 @@ __global__ void k_census(StepParams P, long long n, double t_end, unsigned long 
   }
   warp_add_u64(n_alive, a);
   warp_add_u64(n_unfinished, u);
-  warp_add_f64(e_sum, e);
+  warp_add_energy(P, EB_CENSUS, e);
 }
 void launch_census(const StepParams &P, long long n, double t_end, unsigned long long *n_alive,
                    unsigned long long *n_unfinished, double *e_sum, cudaStream_t st) {
-  if (n > 0) k_census<<<grid_for(n, 256), 256, 0, st>>>(P, n, t_end, n_alive, n_unfinished, e_sum);
+  cudaMemsetAsync(P.ebins + EB_CENSUS * EBINS, 0, sizeof(double) * EBINS, st);
+  if (n > 0) k_census<<<grid_for(n, 256), 256, 0, st>>>(P, n, t_end, n_alive, n_unfinished);
+  launch_fold_bins(P, EB_CENSUS, e_sum, st);
 }
 
 // ---------------------------------------------------------------------------------------

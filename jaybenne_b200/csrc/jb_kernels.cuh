@@ -37,8 +37,17 @@ struct DMesh {
   const int *local_gid;   // [nlocal] -> gid
 };
 
+// what one IMC segment looks up in its cell, packed so it arrives in one 32-byte sector:
+// rho and fleck_factor as stored, temp = EOS temperature of (rho, sie), ss = total scattering
+// coefficient — both evaluated with the very operations the per-segment code would use, once
+// per cell per cycle instead of once per segment (k_pack_props).
+struct __align__(32) CellProps {
+  double rho, temp, ff, ss;
+};
+
 struct Fields {
   double *rho, *sie, *u, *tally, *fleck, *src_ew, *src_num, *edelta;
+  CellProps *props;
   double *fp[3];
   long long nface[3];  // values per block of fp[d]
 };
@@ -78,6 +87,14 @@ struct EventLog {
   unsigned long long *count;  // == &DStats::n_events
 };
 
+// Energy sums (sourced / absorbed / escaped / census) are accumulated per thread, reduced
+// over the warp by shuffles and added to one of EBINS bins chosen by the warp's id, then the
+// bins are folded pairwise (k_fold_bins). A sum over 1e9 photons therefore goes through
+// ~log2 levels of additions of comparable magnitudes instead of 3e7 atomics onto one double,
+// which is what keeps the per-cycle conservation residual below 1e-12 at full size.
+static constexpr int EBINS = 1024;
+enum { EB_SOURCED = 0, EB_ABSORBED = 1, EB_ESCAPED = 2, EB_CENSUS = 3, EB_KINDS = 4 };
+
 struct StepParams {
   DMesh mesh;
   Fields f;
@@ -86,6 +103,7 @@ struct StepParams {
   Outbox out;
   EventLog log;
   DStats *stats;
+  double *ebins;  // [EB_KINDS][EBINS]
   uint32_t key0, key1_particle, key1_cell;
   int use_ddmc;
   double tau_ddmc;
@@ -103,6 +121,17 @@ void launch_source_emit(const StepParams &P, int first_local, int nlocal_call, i
                         double dt, uint32_t call, const long long *prefix, long long slot0, cudaStream_t st);
 void launch_transport(const StepParams &P, long long first, long long n, double t_start, double dt,
                       cudaStream_t st);
+// knobs of the persistent IMC kernel (jb_lib.cu reads them from the environment once)
+struct TransportTuning {
+  int variant;      // 0 = thread-per-photon history kernel, 1 = persistent warps with lane refill
+  int ctas_per_sm;  // 3, 4 or 5 CTAs of 128 threads (168 / 128 / 96 registers per thread)
+  int refill_min;   // refill when at least this many lanes of a warp are idle
+  int validate;     // 1: cross-check the face-crossing index update against Xtoijk (n_error)
+};
+void set_transport_tuning(const TransportTuning &t);
+void launch_pack_props(const StepParams &P, cudaStream_t st);
+// folds ebins[kind] into *dst (dst = &stats->e_* or the census scratch)
+void launch_fold_bins(const StepParams &P, int kind, double *dst, cudaStream_t st);
 void launch_tally(const StepParams &P, long long n, cudaStream_t st);
 void launch_update_fluid(const StepParams &P, cudaStream_t st);
 void launch_update_derived_material(const StepParams &P, cudaStream_t st);

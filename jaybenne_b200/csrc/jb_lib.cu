@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <string>
@@ -84,6 +85,8 @@ struct jb_ctx {
   long long holes_cap = 0;
   unsigned long long *d_counters = nullptr;  // [8] misc device counters
   double *d_esum = nullptr;
+  double *d_ebins = nullptr;          // [EB_KINDS][EBINS] energy-sum bins (jb_kernels.cuh)
+  bool props_dirty = true;            // CellProps must be rebuilt before the next transport
   DStats *d_stats = nullptr;
   DStats *h_stats = nullptr;          // pinned
   unsigned long long *h_counters = nullptr;  // pinned [8 + n_ranks*n_ranks]
@@ -208,6 +211,7 @@ static StepParams make_params(jb_ctx *c) {
   P.log.cap = c->event_cap;
   P.log.count = c->d_stats ? &c->d_stats->n_events : nullptr;
   P.stats = c->d_stats;
+  P.ebins = c->d_ebins;
   P.key0 = (uint32_t)((uint64_t)c->cfg.seed);
   P.key1_particle = (uint32_t)((uint64_t)c->cfg.seed >> 32) ^ STREAM_PARTICLE;
   P.key1_cell = (uint32_t)((uint64_t)c->cfg.seed >> 32) ^ STREAM_CELL;
@@ -297,6 +301,7 @@ jb_status jb_create(const jb_config *cfg, jb_ctx **out) {
   for (auto &e : c->ev) cudaEventCreate(&e);
   bool ok = dalloc(&c->d_stats, 1) == cudaSuccess && dalloc(&c->d_counters, 8) == cudaSuccess &&
             dalloc(&c->d_esum, 2) == cudaSuccess && dalloc(&c->d_total, 2) == cudaSuccess &&
+            dalloc(&c->d_ebins, (long long)EB_KINDS * EBINS) == cudaSuccess &&
             cudaMallocHost((void **)&c->h_stats, sizeof(DStats)) == cudaSuccess &&
             cudaMallocHost((void **)&c->h_counters, sizeof(unsigned long long) * (16 + 64 * 64)) == cudaSuccess;
   if (!ok) {
@@ -304,6 +309,16 @@ jb_status jb_create(const jb_config *cfg, jb_ctx **out) {
     return JB_ERR_CUDA;
   }
   cudaMemset(c->d_stats, 0, sizeof(DStats));
+  cudaMemset(c->d_ebins, 0, sizeof(double) * EB_KINDS * EBINS);
+  // kernel tuning knobs (diagnostics / A-B measurements; defaults are the shipped configuration)
+  {
+    TransportTuning t = {1, 4, 4, 0};
+    if (const char *v = getenv("JB_TRANSPORT_VARIANT")) t.variant = atoi(v);
+    if (const char *v = getenv("JB_IMC_CTAS_PER_SM")) t.ctas_per_sm = atoi(v);
+    if (const char *v = getenv("JB_IMC_REFILL_MIN")) t.refill_min = std::max(1, std::min(32, atoi(v)));
+    if (const char *v = getenv("JB_IMC_VALIDATE")) t.validate = atoi(v);
+    set_transport_tuning(t);
+  }
   *out = c;
   return JB_OK;
 }
@@ -320,7 +335,7 @@ void jb_destroy(jb_ctx *c) {
   for (int d = 0; d < 3; ++d) dfree(c->f.fp[d]);
   dfree(c->d_cnt); dfree(c->d_prefix); dfree(c->d_scan); dfree(c->d_total);
   dfree(c->d_holes); dfree(c->d_tails); dfree(c->d_counters); dfree(c->d_esum); dfree(c->d_stats);
-  dfree(c->d_count_matrix); dfree(c->d_events);
+  dfree(c->d_count_matrix); dfree(c->d_events); dfree(c->d_ebins); dfree(c->f.props);
   if (c->h_stats) cudaFreeHost(c->h_stats);
   if (c->h_counters) cudaFreeHost(c->h_counters);
   for (auto &e : c->ev)
@@ -417,6 +432,8 @@ jb_status jb_set_mesh(jb_ctx *c, const jb_mesh *m, int32_t my_rank, int32_t n_ra
     JB_CUDA(c, dalloc(pp, c->ncells_local));
     JB_CUDA(c, cudaMemset(*pp, 0, sizeof(double) * (size_t)std::max<long long>(c->ncells_local, 1)));
   }
+  JB_CUDA(c, dalloc(&c->f.props, c->ncells_local));
+  c->props_dirty = true;
   c->f.nface[0] = (long long)(m->nxb[0] + 1) * m->nxb[1] * m->nxb[2];
   c->f.nface[1] = (long long)m->nxb[0] * (m->nxb[1] + 1) * m->nxb[2];
   c->f.nface[2] = (long long)m->nxb[0] * m->nxb[1] * (m->nxb[2] + 1);
@@ -470,6 +487,7 @@ jb_status jb_set_field(jb_ctx *c, int32_t gid, int32_t field, const double *src)
   JB_CUDA(c, cudaSetDevice(c->device));
   JB_CUDA(c, cudaMemcpyAsync(p + (size_t)c->gid_to_local[gid] * nb, src, sizeof(double) * nb, cudaMemcpyDefault, c->stream));
   JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->props_dirty = true;
   return JB_OK;
 }
 jb_status jb_get_field(jb_ctx *c, int32_t gid, int32_t field, double *dst) {
@@ -490,6 +508,13 @@ jb_status jb_get_field(jb_ctx *c, int32_t gid, int32_t field, double *dst) {
 
 // ---- internals of the step ---------------------------------------------------------------
 static jb_status sync_stats(jb_ctx *c) {
+  {
+    StepParams P = make_params(c);
+    launch_fold_bins(P, EB_SOURCED, &c->d_stats->e_sourced, c->stream);
+    launch_fold_bins(P, EB_ABSORBED, &c->d_stats->e_absorbed, c->stream);
+    launch_fold_bins(P, EB_ESCAPED, &c->d_stats->e_escaped, c->stream);
+    c->launches += 3;
+  }
   JB_CUDA(c, cudaMemcpyAsync(c->h_stats, c->d_stats, sizeof(DStats), cudaMemcpyDeviceToHost, c->stream));
   JB_CUDA(c, cudaStreamSynchronize(c->stream));
   return JB_OK;
@@ -501,7 +526,7 @@ static jb_status census(jb_ctx *c, double t_end, long long *n_alive, long long *
   JB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * 2, c->stream));
   JB_CUDA(c, cudaMemsetAsync(c->d_esum, 0, sizeof(double), c->stream));
   launch_census(P, c->n, t_end, c->d_counters, c->d_counters + 1, c->d_esum, c->stream);
-  c->launches += c->n > 0;
+  c->launches += 1 + (c->n > 0);
   JB_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(unsigned long long) * 2, cudaMemcpyDeviceToHost, c->stream));
   JB_CUDA(c, cudaMemcpyAsync(c->h_counters + 2, c->d_esum, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   JB_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -570,6 +595,7 @@ static jb_status source_photons(jb_ctx *c, int first, int nb, int source_type, d
 static jb_status stats_begin(jb_ctx *c) {
   memset(&c->stats, 0, sizeof(c->stats));
   JB_CUDA(c, cudaMemsetAsync(c->d_stats, 0, sizeof(DStats), c->stream));
+  JB_CUDA(c, cudaMemsetAsync(c->d_ebins, 0, sizeof(double) * EB_KINDS * EBINS, c->stream));
   long long na = 0;
   double e = 0.0;
   jb_status s = census(c, 0.0, &na, nullptr, &e);
@@ -699,6 +725,7 @@ jb_status jb_update_derived_transport_fields(jb_ctx *c, double dt) {
   StepParams P = make_params(c);
   launch_fleck(P, dt, c->stream);
   c->launches += 1;
+  c->props_dirty = true;
   if (c->cfg.use_ddmc) {
     if ((int)c->local_gid.size() != c->mesh.nblocks)
       return fail(c, JB_ERR_UNSUPPORTED, "DDMC face probabilities need every block on one rank (no ghost exchange yet)");
@@ -748,6 +775,11 @@ jb_status jb_initialize_radiation(jb_ctx *c, int32_t is_thermal) {
 // photons that are gone (RemoveMarkedParticles, transport.cpp:176-178).
 static jb_status transport_range(jb_ctx *c, long long first, long long n, double t_start, double dt) {
   StepParams P = make_params(c);
+  if (c->props_dirty && !c->cfg.use_ddmc) {  // rho, sie or fleck_factor changed since the records were packed
+    launch_pack_props(P, c->stream);
+    c->launches += 1;
+    c->props_dirty = false;
+  }
   launch_transport(P, first, n, t_start, dt, c->stream);
   c->launches += n > 0;
   JB_CUDA(c, cudaGetLastError());
@@ -807,6 +839,7 @@ jb_status jb_update_derived_material(jb_ctx *c) {
   StepParams P = make_params(c);
   launch_update_derived_material(P, c->stream);
   c->launches += 1;
+  c->props_dirty = true;
   JB_CUDA(c, cudaGetLastError());
   return JB_OK;
 }

@@ -24,9 +24,13 @@ def run_pair(gpu, ora, cycles, density_fn=None, fields=True, exact=True):
         pu.assert_stats_equal(sg, so)
         assert pu.conservation_residual(sg) <= 1e-12, pu.conservation_residual(sg)
         assert abs(pu.conservation_residual(sg) - pu.conservation_residual(so)) <= 1e-12
-        pu.assert_swarm_equal(gpu.jb, ora.jb, exact=exact)
+        # with material feedback the next cycle's source weights inherit the last bits of the
+        # energy_delta sums, whose order differs (atomics): bit-exact only while nothing feeds back
+        fed_back = c > 0 and gpu.cfg.do_feedback and sg["n_absorbed"] + sg["n_sourced"] > 0
+        pu.assert_swarm_equal(gpu.jb, ora.jb, exact=exact and not fed_back)
         if fields:
-            pu.assert_fields_equal(gpu, ora)
+            ncells = gpu.mesh.nblocks * int(np.prod(gpu.jb.nxb))
+            pu.assert_fields_equal(gpu, ora, gross=(so["e_sourced"] + so["e_absorbed"]) / ncells)
     return sg, so
 
 
@@ -90,3 +94,116 @@ def test_outflow_escape():
     gpu, ora = pu.make_pair(text=text)
     sg, _ = run_pair(gpu, ora, cycles=1)
     assert sg["n_escaped"] > 0
+
+
+# ---- DDMC / hybrid ---------------------------------------------------------------------------
+def test_stepdiff_ddmc_ci():
+    gpu, ora = pu.make_pair("stepdiff_ddmc", ci=True, overrides=[("jaybenne", "num_particles", 4000)])
+    sg, _ = run_pair(gpu, ora, cycles=2, fields=False)
+    assert sg["n_ddmc_segments"] == sg["n_segments"] > 0
+
+
+def test_inf_stiff_ddmc_with_emission():
+    gpu, ora = pu.make_pair("inf_stiff", overrides=[("jaybenne", "num_particles", 2000)])
+    sg, _ = run_pair(gpu, ora, cycles=3)
+    assert sg["n_ddmc_segments"] > 0 and sg["n_absorbed"] > 0 and sg["n_sourced"] > 0
+
+
+def test_stepdiff_smr_ddmc_ci_block_face_resampling():
+    gpu, ora = pu.make_pair("stepdiff_smr_ddmc", ci=True, overrides=[("jaybenne", "num_particles", 8000)])
+    sg, _ = run_pair(gpu, ora, cycles=2, fields=False)
+    assert sg["n_block_crossings"] > 0 and sg["n_ddmc_segments"] > 0
+    for gid in gpu.jb.local_gids[:6]:
+        for d in ("x1", "x2"):
+            a, b = gpu.jb.get_field(gid, "ddmc_face_prob_" + d), ora.jb.get_field(gid, "ddmc_face_prob_" + d)
+            assert np.array_equal(a, b), (gid, d)
+
+
+def test_stepdiff_smr_hybrid_shipped_resolution_true_hybrid():
+    gpu, ora = pu.make_pair("stepdiff_smr_hybrid", overrides=[("jaybenne", "num_particles", 8000)])
+    sg, _ = run_pair(gpu, ora, cycles=1, fields=False)
+    assert 0 < sg["n_ddmc_segments"] < sg["n_segments"]      # IMC in the fine region, DDMC outside
+
+
+def test_synthetic_3d_ddmc_thick():
+    text = pu.synthetic_text(n=8, nb=4, num_particles=6000, kappa=8.0, sigma=80.0,
+                             extra="").replace("<jaybenne>", "<jaybenne>\nuse_ddmc = true\ntau_ddmc = 5.0")
+    gpu, ora = pu.make_pair(text=text)
+    sg, _ = run_pair(gpu, ora, cycles=2, density_fn=pu.synthetic_density)
+    assert sg["n_ddmc_segments"] > 0
+
+
+# ---- the committed golden fixtures (reference headers) against the CUDA path ------------------
+def test_cuda_path_against_reference_golden_runs():
+    import json, os
+    import golden_cases as gc
+    from jaybenne_b200 import device_api
+    want = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "runs.json")))
+    got = gc.run_table(device_api())
+    for name, w in want.items():
+        if name.startswith("_"):
+            continue
+        g = got[name]
+        assert g["nblocks"] == w["nblocks"] and g["n_init"] == w["n_init"], name
+        for cyc, (gr, wr) in enumerate(zip(g["cycles"], w["cycles"])):
+            for k in gc.COUNT_KEYS:
+                assert gr[k] == wr[k], (name, cyc, k, gr[k], wr[k])
+            for k in gc.ENERGY_KEYS + ("tally_sum",):
+                a, b = gc.unhex(gr[k]), gc.unhex(wr[k])
+                assert abs(a - b) <= 1e-12 * max(abs(a), abs(b), 1e-300), (name, cyc, k)
+
+
+# ---- other closures -----------------------------------------------------------------------------
+def test_epbremss_thomson_closures():
+    text = pu.synthetic_text(n=8, nb=4, num_particles=3000)
+    text = text.replace("opacity_model = constant", "opacity_model = ep_bremss").replace(
+        "initial_temperature = 1.0", "initial_temperature = 1.0e8").replace("initial_density = 1.0", "initial_density = 1.0e-12")
+    # free-free absorption ~ 26 / cm at the Planck-sampled "frequencies", Thomson scattering ~ 10 / cm
+    gpu, ora = pu.make_pair(text=text, cfg_overrides={"scattering_model": 1, "apm": 3.3e-38})
+    run_pair(gpu, ora, cycles=2)
+
+
+# ---- reference acceptance + size-independent properties at scale --------------------------------
+def test_stepdiff_analytic_acceptance_full():
+    """tst/stepdiff.py as the CI runs it: 128 cells, 1e5 photons, 10 cycles, tolerance 0.05."""
+    import regression_util as ru
+    from jaybenne_b200 import Mcblock, device_api
+    mb = Mcblock(pu.make_pin("stepdiff", ci=True), api=device_api())
+    mb.ProblemGenerator()
+    mb.Execute()
+    assert mb.ncycle == 10
+    err = ru.weighted_mean_frac_error(mb.dump())
+    assert err <= ru.TOL_STEPDIFF, err
+
+
+def test_stepdiff_smr_analytic_acceptance_full():
+    """tst/stepdiff_smr.py: 64x32 base, 16x16 blocks, tolerance 0.3 — IMC, DDMC and hybrid decks."""
+    import regression_util as ru
+    from jaybenne_b200 import Mcblock, device_api
+    for deck in ("stepdiff_smr", "stepdiff_smr_ddmc", "stepdiff_smr_hybrid"):
+        mb = Mcblock(pu.make_pin(deck, ci=True), api=device_api())
+        mb.ProblemGenerator()
+        mb.Execute()
+        err = ru.weighted_mean_frac_error(mb.dump())
+        assert err <= ru.TOL_STEPDIFF_SMR, (deck, err)
+
+
+def test_large_run_conservation_and_count_identities():
+    """128^3 cells / 1.25e8 photons (the single-GPU twin of the BASELINE workload): properties
+    that do not need the oracle — energy conservation to 1e-12, photon bookkeeping, tally sum."""
+    from jaybenne_b200 import Mcblock, device_api
+    n = 128
+    text = pu.synthetic_text(n=n, nb=32, num_particles=int(1.25e8))
+    mb = Mcblock(pu.make_pin(text=text), api=device_api(), capacity=int(1.3e8), cfg_overrides={"source_nblocks": 64})
+    mb.ProblemGenerator(pu.synthetic_density)
+    for _ in range(2):
+        st = mb.Step()
+        mb.time += mb.dt
+        assert pu.conservation_residual(st) <= 1e-12, pu.conservation_residual(st)
+        assert st["n_end"] == st["n_start"] + st["n_sourced"] - st["n_absorbed"] - st["n_escaped"]
+        assert st["n_iterations"] == 1 and st["n_segments"] > 5 * st["n_start"]
+        dv = (1.0 / n) ** 3
+        tally = sum(mb.jb.get_field(g, "energy_tally").sum() for g in mb.jb.local_gids) * dv
+        assert abs(tally - st["e_end"]) <= 1e-11 * st["e_end"]
+        edelta = sum(mb.jb.get_field(g, "energy_delta").sum() for g in mb.jb.local_gids)
+        assert abs(edelta - (st["e_absorbed"] - st["e_sourced"])) <= 1e-9 * st["e_absorbed"]
