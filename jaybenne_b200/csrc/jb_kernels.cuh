@@ -27,6 +27,13 @@ struct DBlock {
   int level, lx[3], rank, local, gid, pad;
 };
 
+// what a segment needs of its meshblock, one 64-byte line: (xmin0[d], dx[d]) pairs so each
+// direction arrives in one 16-byte load, and the smallest cell width (the step cap)
+struct __align__(16) BlkGeo {
+  double2 xd[3];
+  double dx_push, pad;
+};
+
 struct DMesh {
   int ndim, nxb[3], ng[3], nlat[3], nrb[3];
   int max_level, nblocks, nlocal, my_rank, n_ranks, ncell;
@@ -35,6 +42,11 @@ struct DMesh {
   const DBlock *blocks;   // [nblocks]
   const int *lattice;     // [nlat2][nlat1][nlat0] -> gid
   const int *local_gid;   // [nlocal] -> gid
+  const BlkGeo *geo;      // [nblocks]
+  // [nlocal][27] gid of the same-level block at offset (bx, by, bz) in {-1,0,1}^3, index
+  // (bz+1)*9 + (by+1)*3 + (bx+1), periodic swarm boundaries wrapped; -1 where the neighbour
+  // is on another level, or beyond a non-periodic domain face (-> find_block path)
+  const int *nbr;
 };
 
 // what one IMC segment looks up in its cell, packed so it arrives in one 32-byte sector:

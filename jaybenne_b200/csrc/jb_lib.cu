@@ -69,7 +69,8 @@ struct jb_ctx {
 
   // device tables
   DBlock *d_blocks = nullptr;
-  int *d_lattice = nullptr, *d_local_gid = nullptr;
+  int *d_lattice = nullptr, *d_local_gid = nullptr, *d_nbr = nullptr;
+  BlkGeo *d_geo = nullptr;
   Fields f{};
   long long ncells_local = 0;
   Swarm s{};
@@ -203,6 +204,8 @@ static StepParams make_params(jb_ctx *c) {
   m.blocks = c->d_blocks;
   m.lattice = c->d_lattice;
   m.local_gid = c->d_local_gid;
+  m.geo = c->d_geo;
+  m.nbr = c->d_nbr;
   P.f = c->f;
   P.s = c->s;
   P.cl = c->cl;
@@ -329,7 +332,7 @@ void jb_destroy(jb_ctx *c) {
   cudaDeviceSynchronize();
   if (c->comm && nccl_api().ok) nccl_api().CommDestroy(c->comm);
   free_swarm(c);
-  dfree(c->d_blocks); dfree(c->d_lattice); dfree(c->d_local_gid);
+  dfree(c->d_blocks); dfree(c->d_lattice); dfree(c->d_local_gid); dfree(c->d_nbr); dfree(c->d_geo);
   dfree(c->f.rho); dfree(c->f.sie); dfree(c->f.u); dfree(c->f.tally); dfree(c->f.fleck);
   dfree(c->f.src_ew); dfree(c->f.src_num); dfree(c->f.edelta);
   for (int d = 0; d < 3; ++d) dfree(c->f.fp[d]);
@@ -427,6 +430,53 @@ jb_status jb_set_mesh(jb_ctx *c, const jb_mesh *m, int32_t my_rank, int32_t n_ra
   JB_CUDA(c, cudaMemcpy(c->d_lattice, lattice.data(), sizeof(int) * lattice.size(), cudaMemcpyHostToDevice));
   if (nl > 0)
     JB_CUDA(c, cudaMemcpy(c->d_local_gid, c->local_gid.data(), sizeof(int) * nl, cudaMemcpyHostToDevice));
+  {
+    // per-block geometry line and the same-level neighbour table of the persistent IMC kernel
+    std::vector<BlkGeo> geo(m->nblocks);
+    for (int g = 0; g < m->nblocks; ++g) {
+      const DBlock &D = hb[g];
+      for (int d = 0; d < 3; ++d) geo[g].xd[d] = make_double2(D.xmin0[d], D.dx[d]);
+      geo[g].dx_push = std::min(D.dx[0], std::min(D.dx[1], D.dx[2]));
+      geo[g].pad = 0.0;
+    }
+    std::vector<int> nbr((size_t)std::max<long long>(nl, 1) * 27, -1);
+    for (long long q = 0; q < nl; ++q) {
+      const DBlock &D = hb[c->local_gid[q]];
+      const int s = 1 << (m->max_level - D.level);
+      for (int bz = -1; bz <= 1; ++bz)
+        for (int by = -1; by <= 1; ++by)
+          for (int bx = -1; bx <= 1; ++bx) {
+            const int off[3] = {bx, by, bz};
+            int tl[3] = {0, 0, 0};
+            bool ok = true;
+            for (int d = 0; d < 3 && ok; ++d) {
+              if (d >= m->ndim) {
+                ok = off[d] == 0;
+                continue;
+              }
+              const int nbl = m->nrb[d] << D.level;  // blocks per dimension at this level
+              int t = D.lx[d] + off[d];
+              if (t < 0) {
+                ok = m->swarm_bc[2 * d] == JB_BC_PERIODIC;
+                t += nbl;
+              } else if (t >= nbl) {
+                ok = m->swarm_bc[2 * d + 1] == JB_BC_PERIODIC;
+                t -= nbl;
+              }
+              tl[d] = t;
+            }
+            if (!ok) continue;
+            const int g = lattice[((size_t)(tl[2] * s) * c->nlat[1] + (size_t)(tl[1] * s)) * c->nlat[0] + (size_t)(tl[0] * s)];
+            const DBlock &N = hb[g];
+            if (N.level == D.level && N.lx[0] == tl[0] && N.lx[1] == tl[1] && N.lx[2] == tl[2])
+              nbr[(size_t)q * 27 + (bz + 1) * 9 + (by + 1) * 3 + (bx + 1)] = g;
+          }
+    }
+    JB_CUDA(c, dalloc(&c->d_geo, m->nblocks));
+    JB_CUDA(c, cudaMemcpy(c->d_geo, geo.data(), sizeof(BlkGeo) * geo.size(), cudaMemcpyHostToDevice));
+    JB_CUDA(c, dalloc(&c->d_nbr, (long long)nbr.size()));
+    JB_CUDA(c, cudaMemcpy(c->d_nbr, nbr.data(), sizeof(int) * nbr.size(), cudaMemcpyHostToDevice));
+  }
   double **cellf[8] = {&c->f.rho, &c->f.sie, &c->f.u, &c->f.tally, &c->f.fleck, &c->f.src_ew, &c->f.src_num, &c->f.edelta};
   for (auto pp : cellf) {
     JB_CUDA(c, dalloc(pp, c->ncells_local));

@@ -5,19 +5,25 @@
 // ptcl_transport_step / scatter (transport_utils.hpp:111-160, scattering.hpp:21-29), the swarm
 // boundary conditions (boundaries.hpp:24-84) and the block hand-over (jaybenne.cpp:26-61).
 //
-// Why it looks the way it does (profiles/r01_v1_ncu_transport_cells64.md): with one thread
-// per photon, 32 histories of very different length share a warp and the warp runs at
-// 14.6 / 32 active lanes. Here a warp owns a contiguous range of swarm slots and keeps every
-// lane busy: a lane whose photon reached census, was absorbed or left the rank stores its
-// result and takes the next slot of the range (ballot + prefix rank), so the segment body
-// always runs close to 32 wide. The FP64 work per segment is cut without changing a single
-// rounding: (1) rho / temperature / fleck / sigma_s come as one 32-byte CellProps record
-// evaluated once per cell per cycle; (2) h*nu and 2 h nu^3 / c^2 are hoisted per photon;
-// (3) the cell index after a step follows from which face nudge fired instead of three more
-// floor((x - xmin) / dx) — ptcl_transport_step leaves a photon either eps_imc_offset cell
-// widths beyond exactly one face per direction or at least that far inside, and rounding is
-// seven orders of magnitude below that margin (VALIDATE re-derives the index with Xtoijk and
-// counts disagreements into n_error; tests/test_parity_gpu.py runs it).
+// Why it looks the way it does (profiles/r01_v1_*.md, r01_v2_*.md):
+//  * one thread per photon ran 14.6 / 32 lanes wide (history lengths differ) -> a warp owns a
+//    contiguous range of swarm slots and refills idle lanes from it (ballot + prefix rank);
+//  * v2 still ran 18.8 / 32 wide because of divergence INSIDE a segment, removed here without
+//    changing a single rounding:
+//      - Philox in lock step: every segment consumes exactly two draws, so every lane evaluates
+//        exactly one Philox block per segment (block (n+1)>>1); a lane whose draw counter is odd
+//        carries the unused half of its previous block (Rng2);
+//      - the vx>0 / vx<0 face-distance branches are one select + one divide per direction;
+//      - a photon that leaves its meshblock through a face shared with a same-level block takes
+//        the neighbour from a 27-entry table and shifts its cell index by the block size (the
+//        general find_block + Xtoijk path remains for level changes and non-periodic faces);
+//      - a photon is loaded with the cell index stored in the swarm instead of three divides;
+//  * the kernel is latency bound (time ~ 1 / resident warps), so per-lane state is kept small:
+//    the meshblock geometry is re-read per segment from a 64-byte BlkGeo line (L1-resident, a
+//    warp's photons share a block) instead of living in 28 registers, weight and energy are
+//    re-read on the rare paths that need them.
+// VALIDATE re-derives every cell index / block with Xtoijk / find_block and counts
+// disagreements into n_error (tests/test_parity_gpu.py runs it).
 #ifndef JAYBENNE_B200_JB_TRANSPORT_IMC_CUH_
 #define JAYBENNE_B200_JB_TRANSPORT_IMC_CUH_
 
@@ -32,13 +38,131 @@ __device__ __forceinline__ CellProps load_props(const CellProps *p) {
   return c;
 }
 
+// The photon's Philox stream (same streams as Rng in jb_device.cuh) consumed two draws at a
+// time. Invariant: when n is odd, (clo, chi) are words 2, 3 of block n >> 1, i.e. draw #n.
+struct Rng2 {
+  uint32_t id0, id1, id2, n, clo, chi;
+
+  __device__ __forceinline__ void block(uint32_t blk, uint32_t k0, uint32_t k1, uint32_t &w0, uint32_t &w1,
+                                        uint32_t &w2, uint32_t &w3) const {
+    uint32_t c0 = blk, c1 = id0, c2 = id1, c3 = id2, a = k0, b = k1;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+      const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+      const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+      c0 = hi1 ^ c1 ^ a;
+      c1 = lo1;
+      c2 = hi0 ^ c3 ^ b;
+      c3 = lo0;
+      a += 0x9E3779B9u;
+      b += 0xBB67AE85u;
+    }
+    w0 = c0; w1 = c1; w2 = c2; w3 = c3;
+  }
+  __device__ __forceinline__ void load(uint32_t a, uint32_t b, uint32_t c, uint32_t draws, uint32_t k0, uint32_t k1) {
+    id0 = a; id1 = b; id2 = c; n = draws; clo = chi = 0u;
+    if (draws & 1u) {
+      uint32_t w0, w1;
+      block(draws >> 1, k0, k1, w0, w1, clo, chi);
+    }
+  }
+  static __device__ __forceinline__ double to_double(uint32_t lo, uint32_t hi) {
+    const uint64_t u = ((uint64_t)hi << 32) | lo;
+    return (double)(u >> 11) * 1.1102230246251565e-16;
+  }
+  // draws #n and #n+1
+  __device__ __forceinline__ void draw2(uint32_t k0, uint32_t k1, double &a, double &b) {
+    uint32_t w0, w1, w2, w3;
+    block((n + 1u) >> 1, k0, k1, w0, w1, w2, w3);
+    const bool odd = (n & 1u) != 0;
+    a = to_double(odd ? clo : w0, odd ? chi : w1);
+    b = to_double(odd ? w0 : w2, odd ? w1 : w3);
+    clo = w2;  // only meaningful while n is odd
+    chi = w3;
+    n += 2u;
+  }
+};
+
+// ptcl_transport_step (transport_utils.hpp:111-160) with the two draws handed in and the
+// face-distance branches written as selects. Operation for operation the arithmetic of
+// imc_step_idx (jb_device.cuh): a direction with v == 0 computes an unused quotient.
+template <int NDIM>
+__device__ __forceinline__ void imc_step_lockstep(const double xi_abs, const double xi_sc, const double t_end,
+                                                  const CellEnv &c, const double vv, const double dx_cell, Photon &p,
+                                                  bool &is_absorbed, bool &is_scattered, int &di, int &dj, int &dk) {
+  constexpr bool multi_d = NDIM >= 2, three_d = NDIM == 3;
+  const double rmin = DBL_MIN;
+  const double lam_abs = 1.0 / (c.ff * c.aa + rmin);
+  const double lam_sc = 1.0 / (c.ss + (1.0 - c.ff) * c.aa + rmin);
+  const double dx_abs = -lam_abs * jbm::log(xi_abs);
+  const double dx_sc = -lam_sc * jbm::log(xi_sc);
+  const double dx_end = vv * (t_end - p.t);
+  double dx_push = jbm::min2(dx_cell, dx_end);
+  {
+    const double face = p.vx > 0.0 ? c.xu : c.xl;
+    const double d = vv * (face - p.x) / p.vx;
+    const double dm = jbm::min2(dx_push, d);
+    dx_push = (p.vx != 0.0) ? dm : dx_push;
+  }
+  if (multi_d) {
+    const double face = p.vy > 0.0 ? c.yu : c.yl;
+    const double d = vv * (face - p.y) / p.vy;
+    const double dm = jbm::min2(dx_push, d);
+    dx_push = (p.vy != 0.0) ? dm : dx_push;
+  }
+  if (three_d) {
+    const double face = p.vz > 0.0 ? c.zu : c.zl;
+    const double d = vv * (face - p.z) / p.vz;
+    const double dm = jbm::min2(dx_push, d);
+    dx_push = (p.vz != 0.0) ? dm : dx_push;
+  }
+  is_absorbed = ((dx_abs < dx_push) && (dx_abs < dx_sc));
+  is_scattered = (!is_absorbed && (dx_sc < dx_push));
+  const double dt_push = (is_absorbed ? dx_abs : (is_scattered ? dx_sc : dx_push)) / vv;
+  p.t += dt_push;
+  p.x += p.vx * dt_push;
+  p.y += (multi_d ? 1.0 : 0.0) * p.vy * dt_push;
+  p.z += (three_d ? 1.0 : 0.0) * p.vz * dt_push;
+  const double fdx = EPS_IMC * (c.xu - c.xl);
+  const double fdy = EPS_IMC * (c.yu - c.yl);
+  const double fdz = EPS_IMC * (c.zu - c.zl);
+  const bool nxl = fabs(p.x - c.xl) < fdx;
+  p.x = nxl ? c.xl - fdx : p.x;
+  const bool nxu = fabs(p.x - c.xu) < fdx;
+  p.x = nxu ? c.xu + fdx : p.x;
+  const bool nyl = multi_d && fabs(p.y - c.yl) < fdy;
+  p.y = nyl ? c.yl - fdy : p.y;
+  const bool nyu = multi_d && fabs(p.y - c.yu) < fdy;
+  p.y = nyu ? c.yu + fdy : p.y;
+  const bool nzl = three_d && fabs(p.z - c.zl) < fdz;
+  p.z = nzl ? c.zl - fdz : p.z;
+  const bool nzu = three_d && fabs(p.z - c.zu) < fdz;
+  p.z = nzu ? c.zu + fdz : p.z;
+  di = nxu ? 1 : (nxl ? -1 : 0);
+  dj = nyu ? 1 : (nyl ? -1 : 0);
+  dk = nzu ? 1 : (nzl ? -1 : 0);
+}
+
+// isotropic scatter (scattering.hpp:21-29) from two draws
+__device__ __forceinline__ void scatter_iso2(const double xi_mu, const double xi_phi, const double vv, double &vx,
+                                             double &vy, double &vz) {
+  const double mu = 2.0 * xi_mu - 1.0;
+  const double phi = 2.0 * JB_PI * xi_phi;
+  const double stheta = sqrt(1.0 - mu * mu);
+  double sn, cs;
+  jbm::sincos(phi, &sn, &cs);
+  vx = vv * stheta * cs;
+  vy = vv * stheta * sn;
+  vz = vv * mu;
+}
+
 template <int NDIM, int MINB, bool VALIDATE>
 __global__ void __launch_bounds__(IMC_TPB, MINB)
     k_transport_imc(StepParams P, long long first, long long n, double t_start, double dt, int refill_min) {
   const DMesh &m = P.mesh;
   const double t_end = t_start + dt;
   const double vv = P.cl.c_code;
-  const int nx1 = m.nxb[0], nx2 = m.nxb[1];
+  const int nx1 = m.nxb[0], nx2 = m.nxb[1], nx3 = m.nxb[2];
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31u;
   const unsigned lt_mask = (1u << lane) - 1u;
@@ -53,17 +177,13 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
   bool have = false;     // this lane holds a photon in flight
   long long idx = 0;     // its slot
   Photon p;
-  double ww = 0.0;
   PhotonFreq q;
-  Rng rng;
-  BlkReg B;
+  Rng2 rng;
+  int gid = 0, lb = 0;   // its meshblock
   p.x = p.y = p.z = p.t = p.vx = p.vy = p.vz = 0.0;
   p.ip = p.jp = p.kp = 0;
   q.f = q.hnu = q.bpref = 0.0;
-  rng.init(0, 0, 0, 0, P.key0, P.key1_particle);
-  B.lb = 0; B.gid = 0; B.dx_push = 0.0;
-#pragma unroll
-  for (int d = 0; d < 3; ++d) B.xmin[d] = B.xmax[d] = B.dx[d] = B.xmin0[d] = 0.0;
+  rng.id0 = rng.id1 = rng.id2 = rng.n = rng.clo = rng.chi = 0u;
 
   unsigned c_seg = 0, c_scat = 0, c_cross = 0, c_abs = 0, c_dead = 0;
   double e_abs = 0.0;
@@ -78,20 +198,31 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
       const long long my = cur + __popc(need & lt_mask);
       cur += cnt;
       if (!have && my < end) {
-        const int lb = P.s.loc[my].x;
-        if (lb >= 0) {
+        const int2 lc = P.s.loc[my];
+        if (lc.x >= 0) {
           const double t0 = P.s.t[my];
           if (t0 < t_end) {  // census photons of an earlier iteration are skipped (transport.cpp:98)
             idx = my;
             p.t = t0;
             p.x = P.s.x[my]; p.y = P.s.y[my]; p.z = P.s.z[my];
             p.vx = P.s.vx[my]; p.vy = P.s.vy[my]; p.vz = P.s.vz[my];
-            ww = P.s.w[my];
             q = photon_freq(P.cl, P.s.e[my]);
             const uint2 ia = P.s.ida[my], ib = P.s.idb[my];
-            rng.init(ia.x, ia.y, ib.x, ib.y, P.key0, P.key1_particle);
-            load_block(m, m.local_gid[lb], B);
-            xtoijk<NDIM>(B, p, p.ip, p.jp, p.kp);
+            rng.load(ia.x, ia.y, ib.x, ib.y, P.key0, P.key1_particle);
+            lb = lc.x;
+            gid = m.local_gid[lb];
+            // the stored flat cell is what Xtoijk (transport.cpp:96) returns for a photon at rest
+            p.ip = lc.y % nx1;
+            const int rest = lc.y / nx1;
+            p.jp = rest % nx2;
+            p.kp = rest / nx2;
+            if (VALIDATE) {
+              BlkReg B;
+              load_block(m, gid, B);
+              int ti, tj, tk;
+              xtoijk<NDIM>(B, p, ti, tj, tk);
+              if (ti != p.ip || tj != p.jp || tk != p.kp) atomicAdd(&P.stats->n_error, 1ull);
+            }
             have = true;
           }
         }
@@ -102,22 +233,32 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
     if (have) {
       // ---- one segment of the while (t < t_end) loop, transport.cpp:112-171 ------------
       c_seg++;
+      double xi_abs, xi_sc;
+      rng.draw2(P.key0, P.key1_particle, xi_abs, xi_sc);
+      const BlkGeo *geo = m.geo + gid;
+      const double2 gx = __ldg(&geo->xd[0]), gy = __ldg(&geo->xd[1]), gz = __ldg(&geo->xd[2]);
+      const double dx_cell = __ldg(&geo->dx_push);
+      const long long ci = (long long)lb * m.ncell + ((long long)p.kp * nx2 + p.jp) * nx1 + p.ip;
+      const CellProps cp = load_props(P.f.props + ci);
       CellEnv c;
       {
-        const double xcen = xc(B, m.ng[0], 0, p.ip), ycen = xc(B, m.ng[1], 1, p.jp), zcen = xc(B, m.ng[2], 2, p.kp);
-        c.xl = xcen - 0.5 * B.dx[0]; c.xu = xcen + 0.5 * B.dx[0];
-        c.yl = ycen - 0.5 * B.dx[1]; c.yu = ycen + 0.5 * B.dx[1];
-        c.zl = zcen - 0.5 * B.dx[2]; c.zu = zcen + 0.5 * B.dx[2];
+        // coords.Xc<d>(i) -/+ dx/2 (transport.cpp:114-119), Xc as UniformCartesian computes it
+        const double xcen = gx.x + ((p.ip + m.ng[0]) + 0.5) * gx.y;
+        const double ycen = gy.x + ((p.jp + m.ng[1]) + 0.5) * gy.y;
+        const double zcen = gz.x + ((p.kp + m.ng[2]) + 0.5) * gz.y;
+        c.xl = xcen - 0.5 * gx.y; c.xu = xcen + 0.5 * gx.y;
+        c.yl = ycen - 0.5 * gy.y; c.yu = ycen + 0.5 * gy.y;
+        c.zl = zcen - 0.5 * gz.y; c.zu = zcen + 0.5 * gz.y;
       }
-      const long long ci = (long long)B.lb * m.ncell + ((long long)p.kp * nx2 + p.jp) * nx1 + p.ip;
-      const CellProps cp = load_props(P.f.props + ci);
       c.ff = cp.ff;
       c.ss = cp.ss;
       c.aa = absorption_coeff_hoisted(P.cl, cp.rho, cp.temp, q);
       bool is_absorbed = false, is_scattered = false;
       int di, dj, dk;
-      imc_step_idx<NDIM>(rng, t_end, c, vv, B.dx_push, p, is_absorbed, is_scattered, di, dj, dk);
+      imc_step_lockstep<NDIM>(xi_abs, xi_sc, t_end, c, vv, dx_cell, p, is_absorbed, is_scattered, di, dj, dk);
       if (VALIDATE) {
+        BlkReg B;
+        load_block(m, gid, B);
         int ti, tj, tk;
         xtoijk<NDIM>(B, p, ti, tj, tk);
         if (ti != p.ip + di || tj != p.jp + dj || tk != p.kp + dk) atomicAdd(&P.stats->n_error, 1ull);
@@ -126,27 +267,50 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
       bool gone = false;
       if (!on_block(m, p.ip, p.jp, p.kp)) {
         // ---- left the meshblock: swarm BCs + hand-over (MeshSend / MeshReceive on device) ----
+        const int bx = p.ip < 0 ? -1 : (p.ip >= nx1 ? 1 : 0);
+        const int by = p.jp < 0 ? -1 : (p.jp >= nx2 ? 1 : 0);
+        const int bz = p.kp < 0 ? -1 : (p.kp >= nx3 ? 1 : 0);
         if (!apply_swarm_bc<NDIM>(m, p)) {
           atomicAdd(&P.stats->n_escaped, 1ull);
-          atomicAdd(&P.ebins[EB_ESCAPED * EBINS + (unsigned)(gw & (EBINS - 1))], ww);
+          atomicAdd(&P.ebins[EB_ESCAPED * EBINS + (unsigned)(gw & (EBINS - 1))], P.s.w[idx]);
           gone = true;
         } else {
-          const double pos[3] = {p.x, p.y, p.z};
-          const int gid = find_block(m, pos);
-          if (gid < 0) {
+          int ngid = __ldg(&m.nbr[lb * 27 + (bz + 1) * 9 + (by + 1) * 3 + (bx + 1)]);
+          const bool fast = ngid >= 0;
+          if (fast) {
+            // same-level neighbour: the photon sits eps_imc_offset cell widths inside it
+            p.ip -= bx * nx1; p.jp -= by * nx2; p.kp -= bz * nx3;
+          } else {
+            const double pos[3] = {p.x, p.y, p.z};
+            ngid = find_block(m, pos);
+          }
+          if (VALIDATE && fast) {
+            const double pos[3] = {p.x, p.y, p.z};
+            const int vg = find_block(m, pos);
+            bool bad = vg != ngid;
+            if (!bad) {
+              BlkReg B;
+              load_block(m, vg, B);
+              int ti, tj, tk;
+              xtoijk<NDIM>(B, p, ti, tj, tk);
+              bad = ti != p.ip || tj != p.jp || tk != p.kp;
+            }
+            if (bad) atomicAdd(&P.stats->n_error, 1ull);
+          }
+          if (ngid < 0) {
             atomicAdd(&P.stats->n_error, 1ull);
             gone = true;
           } else {
             c_cross++;
-            const DBlock &nb = m.blocks[gid];
+            const DBlock &nb = m.blocks[ngid];
             if (nb.rank != m.my_rank) {
               const unsigned long long slot = atomicAdd(&P.out.count[nb.rank], 1ull);
               if ((long long)slot < P.out.cap) {
                 ExRecord r;
-                r.x = p.x; r.y = p.y; r.z = p.z; r.t = p.t; r.w = ww; r.e = P.s.e[idx];
+                r.x = p.x; r.y = p.y; r.z = p.z; r.t = p.t; r.w = P.s.w[idx]; r.e = P.s.e[idx];
                 r.vx = p.vx; r.vy = p.vy; r.vz = p.vz;
                 r.rng[0] = rng.id0; r.rng[1] = rng.id1; r.rng[2] = rng.id2; r.rng[3] = rng.n;
-                r.dest_gid = gid;
+                r.dest_gid = ngid;
                 r.pad = 0;
                 P.out.rec[(size_t)nb.rank * P.out.cap + slot] = r;
                 atomicAdd(&P.stats->n_sent, 1ull);
@@ -155,18 +319,26 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
               }
               gone = true;
             } else {
-              load_block(m, gid, B);
-              xtoijk<NDIM>(B, p, p.ip, p.jp, p.kp);
+              gid = ngid;
+              lb = nb.local;
+              if (!fast) {
+                BlkReg B;
+                load_block(m, gid, B);
+                xtoijk<NDIM>(B, p, p.ip, p.jp, p.kp);
+              }
             }
           }
         }
       } else if (is_absorbed) {
-        atomicAdd(&P.f.edelta[(long long)B.lb * m.ncell + ((long long)p.kp * nx2 + p.jp) * nx1 + p.ip], ww);
+        const double ww = P.s.w[idx];
+        atomicAdd(&P.f.edelta[(long long)lb * m.ncell + ((long long)p.kp * nx2 + p.jp) * nx1 + p.ip], ww);
         c_abs++;
         e_abs += ww;
         gone = true;
       } else if (is_scattered) {
-        scatter_iso(rng, vv, p.vx, p.vy, p.vz);
+        double xi_mu, xi_phi;
+        rng.draw2(P.key0, P.key1_particle, xi_mu, xi_phi);
+        scatter_iso2(xi_mu, xi_phi, vv, p.vx, p.vy, p.vz);
         c_scat++;
       }
       // ---- photon finished for this call? write it back and free the lane -----------------
@@ -177,7 +349,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
       } else if (!(p.t < t_end)) {
         P.s.x[idx] = p.x; P.s.y[idx] = p.y; P.s.z[idx] = p.z; P.s.t[idx] = p.t;
         P.s.vx[idx] = p.vx; P.s.vy[idx] = p.vy; P.s.vz[idx] = p.vz;
-        P.s.loc[idx] = make_int2(B.lb, (p.kp * nx2 + p.jp) * nx1 + p.ip);
+        P.s.loc[idx] = make_int2(lb, (p.kp * nx2 + p.jp) * nx1 + p.ip);
         P.s.idb[idx] = make_uint2(rng.id2, rng.n);
         have = false;
       }
@@ -221,6 +393,8 @@ static void launch_transport_imc(const StepParams &P, long long first, long long
   switch (g_tuning.ctas_per_sm) {
     case 3: launch_transport_imc_occ<NDIM, 3>(P, first, n, t_start, dt, st); break;
     case 5: launch_transport_imc_occ<NDIM, 5>(P, first, n, t_start, dt, st); break;
+    case 6: launch_transport_imc_occ<NDIM, 6>(P, first, n, t_start, dt, st); break;
+    case 8: launch_transport_imc_occ<NDIM, 8>(P, first, n, t_start, dt, st); break;
     default: launch_transport_imc_occ<NDIM, 4>(P, first, n, t_start, dt, st); break;
   }
 }
