@@ -19,8 +19,8 @@ and photons leaving a rank travel over NCCL inside jb_radiation_step.
           memory every step, energy_tally and internal_energy read back every step.
   roofline  transport kernel (k_transport): algorithmic bytes per launch
           84 B x (photons in + photons out) + 32 B x cells, over its own CUDA-event time.
-  cpu_baseline  the CPU oracle (reference per-particle headers, OpenMP over photons) on a
-          64^3-cell twin of the same workload on the box's host cores (rank 0, N = 1 only).
+  cpu_baseline  the CPU oracle (reference per-particle headers, OpenMP over photons, the
+          reference's XorShift64 pool with one state per thread) on a 64^3-cell twin of the same workload on the box's host cores (rank 0, N = 1 only).
 
 `--impl reference` times that CPU implementation alone (rank 0; other ranks exit 0).
 """
@@ -132,7 +132,7 @@ def cpu_arm(cells, nb, particles, steps, warmup, budget_s=300.0):
     """
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_binding as ob
-    from jaybenne_b200 import Mcblock, ParameterInput
+    from jaybenne_b200 import Mcblock, ParameterInput, capi
     ref_fast = os.path.join(ob.ORACLE_DIR, "_ref", "libjb_oracle_ref_fast.so")
     if os.path.exists(ref_fast):
         ob.FLAVOURS["ref_fast"] = ref_fast
@@ -144,7 +144,8 @@ def cpu_arm(cells, nb, particles, steps, warmup, budget_s=300.0):
 
     def make(cells_, particles_):
         pin = ParameterInput(text=workload_text(cells_, min(nb, cells_), particles_))
-        mb = Mcblock(pin, api=api)
+        # the reference's generator: one XorShift64 pool state per host thread (Kokkos OpenMP backend)
+        mb = Mcblock(pin, api=api, cfg_overrides={"rng_mode": capi.JB_RNG_XORSHIFT_THREADS})
         return mb
 
     def one_step(mb):
@@ -171,7 +172,7 @@ def cpu_arm(cells, nb, particles, steps, warmup, budget_s=300.0):
     el = time.perf_counter() - t0
     info = {"kind": kind, "cores": cores, "flavour": api.flavour().decode(),
             "sample": f"{cells}^3-cell twin of the workload (same per-cell loading), {particles} photons, "
-                      f"{steps} step(s): thermal sourcing + one cycle, OpenMP over photons, Philox streams"}
+                      f"{steps} step(s): thermal sourcing + one cycle, OpenMP over photons, one XorShift64 pool state per thread as in the reference"}
     return seg / el, 1e3 * el / max(steps, 1), info
 
 

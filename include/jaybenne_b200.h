@@ -52,7 +52,10 @@ enum { JB_STRATEGY_UNIFORM = 0, JB_STRATEGY_ENERGY = 1 };
 /* random streams. PHILOX = per-particle counter-based streams (the product).
  * XORSHIFT_POOL = the reference's Kokkos::Random_XorShift64_Pool borrowed in serial
  * order; implemented by the oracle only (the CUDA library rejects it). */
-enum { JB_RNG_PHILOX = 0, JB_RNG_XORSHIFT_POOL = 1 };
+enum { JB_RNG_PHILOX = 0, JB_RNG_XORSHIFT_POOL = 1,
+       /* oracle timing builds only: one XorShift64 pool state per OpenMP thread, which is what
+        * the reference's pool gives the Kokkos OpenMP backend (not reproducible) */
+       JB_RNG_XORSHIFT_THREADS = 2 };
 /* gray absorption evaluation. KIRCHHOFF = the reference's literal j_nu / B_nu round trip
  * (gray_opacity_photons.hpp:50-54); DIRECT = rho*kappa (differs by <= 1 ulp, and where
  * B_nu under/overflows). */

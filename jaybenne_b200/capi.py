@@ -26,7 +26,7 @@ JB_SCAT_GRAY, JB_SCAT_THOMSON = 0, 1
 JB_BC_PERIODIC, JB_BC_REFLECT, JB_BC_OUTFLOW = 0, 1, 2
 JB_SOURCE_THERMAL, JB_SOURCE_EMISSION = 0, 1
 JB_STRATEGY_UNIFORM, JB_STRATEGY_ENERGY = 0, 1
-JB_RNG_PHILOX, JB_RNG_XORSHIFT_POOL = 0, 1
+JB_RNG_PHILOX, JB_RNG_XORSHIFT_POOL, JB_RNG_XORSHIFT_THREADS = 0, 1, 2
 JB_GRAY_KIRCHHOFF, JB_GRAY_DIRECT = 0, 1
 (JB_FIELD_DENSITY, JB_FIELD_SIE, JB_FIELD_INTERNAL_ENERGY, JB_FIELD_ENERGY_TALLY, JB_FIELD_FLECK_FACTOR,
  JB_FIELD_SOURCE_EW_PER_CELL, JB_FIELD_SOURCE_NUM_PER_CELL, JB_FIELD_ENERGY_DELTA, JB_FIELD_DDMC_FACE_PROB_X1,

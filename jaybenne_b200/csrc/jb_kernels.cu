@@ -1002,14 +1002,25 @@ void launch_census(const StepParams &P, long long n, double t_end, unsigned long
 // ---------------------------------------------------------------------------------------
 __global__ void k_compact_find(StepParams P, long long n, long long n_alive, long long *holes, long long *tails,
                                unsigned long long *counters) {
-  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < n;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const bool alive = P.s.loc[idx].x >= 0;
-    if (idx < n_alive) {
-      if (!alive) holes[atomicAdd(&counters[0], 1ull)] = idx;
-    } else {
-      if (alive) tails[atomicAdd(&counters[1], 1ull)] = idx;
+  // one atomic per warp and list: lanes rank themselves inside the ballot
+  const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long base = blockIdx.x * (long long)blockDim.x + (threadIdx.x & ~31u); base < n; base += stride) {
+    const long long idx = base + lane;
+    const bool valid = idx < n;
+    const bool alive = valid && P.s.loc[idx].x >= 0;
+    const bool is_hole = valid && idx < n_alive && !alive;
+    const bool is_tail = valid && idx >= n_alive && alive;
+    const unsigned mh = __ballot_sync(0xffffffffu, is_hole), mt = __ballot_sync(0xffffffffu, is_tail);
+    unsigned long long bh = 0, bt = 0;
+    if (lane == 0) {
+      if (mh) bh = atomicAdd(&counters[0], (unsigned long long)__popc(mh));
+      if (mt) bt = atomicAdd(&counters[1], (unsigned long long)__popc(mt));
     }
+    bh = __shfl_sync(0xffffffffu, bh, 0);
+    bt = __shfl_sync(0xffffffffu, bt, 0);
+    if (is_hole) holes[bh + __popc(mh & lt)] = idx;
+    if (is_tail) tails[bt + __popc(mt & lt)] = idx;
   }
 }
 __global__ void k_compact_move(StepParams P, const long long *holes, const long long *tails,

@@ -136,7 +136,7 @@ void launch_transport(const StepParams &P, long long first, long long n, double 
 // knobs of the persistent IMC kernel (jb_lib.cu reads them from the environment once)
 struct TransportTuning {
   int variant;      // 0 = thread-per-photon history kernel, 1 = persistent warps with lane refill
-  int ctas_per_sm;  // 3, 4 or 5 CTAs of 128 threads (168 / 128 / 96 registers per thread)
+  int ctas_per_sm;  // CTAs of 128 threads per SM: 4, 6 or 8 (default)
   int refill_min;   // refill when at least this many lanes of a warp are idle
   int validate;     // 1: cross-check the face-crossing index update against Xtoijk (n_error)
 };

@@ -315,7 +315,7 @@ jb_status jb_create(const jb_config *cfg, jb_ctx **out) {
   cudaMemset(c->d_ebins, 0, sizeof(double) * EB_KINDS * EBINS);
   // kernel tuning knobs (diagnostics / A-B measurements; defaults are the shipped configuration)
   {
-    TransportTuning t = {1, 4, 4, 0};
+    TransportTuning t = {1, 8, 4, 0};
     if (const char *v = getenv("JB_TRANSPORT_VARIANT")) t.variant = atoi(v);
     if (const char *v = getenv("JB_IMC_CTAS_PER_SM")) t.ctas_per_sm = atoi(v);
     if (const char *v = getenv("JB_IMC_REFILL_MIN")) t.refill_min = std::max(1, std::min(32, atoi(v)));

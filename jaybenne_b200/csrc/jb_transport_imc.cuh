@@ -156,13 +156,20 @@ __device__ __forceinline__ void scatter_iso2(const double xi_mu, const double xi
   vz = vv * mu;
 }
 
-template <int NDIM, int MINB, bool VALIDATE>
+// ABS selects the absorption closure at compile time: 0 = gray through the reference's
+// j_nu / B_nu round trip, 1 = gray as rho * kappa (JB_GRAY_DIRECT), 2 = whatever the
+// Closure says (free-free); 0 and 1 need neither the photon frequency nor the EPBremss code.
+enum { ABS_GRAY_KIRCHHOFF = 0, ABS_GRAY_DIRECT = 1, ABS_GENERIC = 2 };
+
+template <int NDIM, int MINB, bool VALIDATE, int ABS>
 __global__ void __launch_bounds__(IMC_TPB, MINB)
     k_transport_imc(StepParams P, long long first, long long n, double t_start, double dt, int refill_min) {
   const DMesh &m = P.mesh;
   const double t_end = t_start + dt;
   const double vv = P.cl.c_code;
   const int nx1 = m.nxb[0], nx2 = m.nxb[1], nx3 = m.nxb[2];
+  const bool pow2 = (nx1 & (nx1 - 1)) == 0 && (nx2 & (nx2 - 1)) == 0;
+  const int sh1 = pow2 ? __ffs(nx1) - 1 : -1, sh2 = pow2 ? __ffs(nx2) - 1 : 0;
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31u;
   const unsigned lt_mask = (1u << lane) - 1u;
@@ -185,8 +192,15 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
   q.f = q.hnu = q.bpref = 0.0;
   rng.id0 = rng.id1 = rng.id2 = rng.n = rng.clo = rng.chi = 0u;
 
-  unsigned c_seg = 0, c_scat = 0, c_cross = 0, c_abs = 0, c_dead = 0;
-  double e_abs = 0.0;
+  // per-lane counters only for what happens every segment; the rare events (absorption, block
+  // change, removal) count into shared memory so they do not hold registers across the loop
+  unsigned c_seg = 0, c_scat = 0;
+  __shared__ unsigned sh_cnt[3];                // crossings, absorbed, dead
+  __shared__ double sh_eabs[IMC_TPB / 32];      // absorbed energy, one partial sum per warp
+  if (threadIdx.x < 3) sh_cnt[threadIdx.x] = 0u;
+  if (threadIdx.x < IMC_TPB / 32) sh_eabs[threadIdx.x] = 0.0;
+  __syncthreads();
+  const unsigned wic = threadIdx.x >> 5;
 
   for (;;) {
     // ---- refill idle lanes from the warp's range ----------------------------------------
@@ -212,10 +226,16 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
             lb = lc.x;
             gid = m.local_gid[lb];
             // the stored flat cell is what Xtoijk (transport.cpp:96) returns for a photon at rest
-            p.ip = lc.y % nx1;
-            const int rest = lc.y / nx1;
-            p.jp = rest % nx2;
-            p.kp = rest / nx2;
+            if (sh1 >= 0) {  // block sizes that are powers of two (the usual case): shifts
+              p.ip = lc.y & (nx1 - 1);
+              p.jp = (lc.y >> sh1) & (nx2 - 1);
+              p.kp = lc.y >> (sh1 + sh2);
+            } else {
+              p.ip = lc.y % nx1;
+              const int rest = lc.y / nx1;
+              p.jp = rest % nx2;
+              p.kp = rest / nx2;
+            }
             if (VALIDATE) {
               BlkReg B;
               load_block(m, gid, B);
@@ -252,7 +272,18 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
       }
       c.ff = cp.ff;
       c.ss = cp.ss;
-      c.aa = absorption_coeff_hoisted(P.cl, cp.rho, cp.temp, q);
+      if (ABS == ABS_GRAY_DIRECT) {
+        c.aa = ((P.cl.rho_unit * cp.rho) * P.cl.kappa) * P.cl.length_unit;
+      } else if (ABS == ABS_GRAY_KIRCHHOFF) {
+        // absorption_coeff_hoisted() with the gray branch fixed
+        const double r = P.cl.rho_unit * cp.rho, T = P.cl.temp_unit * cp.temp;
+        const double x = q.hnu / (P.cl.kb * T);
+        const double Bnu = q.bpref / jbm::expm1(x);
+        const double jnu = r * P.cl.kappa * Bnu;
+        c.aa = robust_ratio(jnu, Bnu) * P.cl.length_unit;
+      } else {
+        c.aa = absorption_coeff_hoisted(P.cl, cp.rho, cp.temp, q);
+      }
       bool is_absorbed = false, is_scattered = false;
       int di, dj, dk;
       imc_step_lockstep<NDIM>(xi_abs, xi_sc, t_end, c, vv, dx_cell, p, is_absorbed, is_scattered, di, dj, dk);
@@ -301,7 +332,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
             atomicAdd(&P.stats->n_error, 1ull);
             gone = true;
           } else {
-            c_cross++;
+            atomicAdd(&sh_cnt[0], 1u);
             const DBlock &nb = m.blocks[ngid];
             if (nb.rank != m.my_rank) {
               const unsigned long long slot = atomicAdd(&P.out.count[nb.rank], 1ull);
@@ -332,8 +363,8 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
       } else if (is_absorbed) {
         const double ww = P.s.w[idx];
         atomicAdd(&P.f.edelta[(long long)lb * m.ncell + ((long long)p.kp * nx2 + p.jp) * nx1 + p.ip], ww);
-        c_abs++;
-        e_abs += ww;
+        atomicAdd(&sh_cnt[1], 1u);
+        atomicAdd(&sh_eabs[wic], ww);
         gone = true;
       } else if (is_scattered) {
         double xi_mu, xi_phi;
@@ -344,7 +375,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
       // ---- photon finished for this call? write it back and free the lane -----------------
       if (gone) {
         P.s.loc[idx].x = -1;
-        c_dead++;
+        atomicAdd(&sh_cnt[2], 1u);
         have = false;
       } else if (!(p.t < t_end)) {
         P.s.x[idx] = p.x; P.s.y[idx] = p.y; P.s.z[idx] = p.z; P.s.t[idx] = p.t;
@@ -358,17 +389,21 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
   DStats *S = P.stats;
   warp_add_u64(&S->n_segments, c_seg);
   warp_add_u64(&S->n_scatters, c_scat);
-  warp_add_u64(&S->n_crossings, c_cross);
-  warp_add_u64(&S->n_absorbed, c_abs);
-  warp_add_u64(&S->n_dead, c_dead);
-  warp_add_energy(P, EB_ABSORBED, e_abs);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (sh_cnt[0]) atomicAdd(&S->n_crossings, (unsigned long long)sh_cnt[0]);
+    if (sh_cnt[1]) atomicAdd(&S->n_absorbed, (unsigned long long)sh_cnt[1]);
+    if (sh_cnt[2]) atomicAdd(&S->n_dead, (unsigned long long)sh_cnt[2]);
+  }
+  if (lane == 0 && sh_eabs[wic] != 0.0)
+    atomicAdd(&P.ebins[EB_ABSORBED * EBINS + (unsigned)(gw & (EBINS - 1))], sh_eabs[wic]);
 }
 
-static TransportTuning g_tuning = {1, 4, 4, 0};
+static TransportTuning g_tuning = {1, 8, 4, 0};
 void set_transport_tuning(const TransportTuning &t) { g_tuning = t; }
 
-template <int NDIM, int MINB>
-static void launch_transport_imc_occ(const StepParams &P, long long first, long long n, double t_start, double dt,
+template <int NDIM, int MINB, bool VALIDATE>
+static void launch_transport_imc_abs(const StepParams &P, long long first, long long n, double t_start, double dt,
                                      cudaStream_t st) {
   // persistent grid: MINB CTAs on each of the SMs (148 on B200); fewer if the range is short
   static int n_sm = 0;
@@ -382,20 +417,25 @@ static void launch_transport_imc_occ(const StepParams &P, long long first, long 
   const long long need = (n + IMC_TPB - 1) / IMC_TPB;
   if (blocks > need) blocks = need;
   if (blocks < 1) blocks = 1;
-  if (g_tuning.validate)
-    k_transport_imc<NDIM, MINB, true><<<(unsigned)blocks, IMC_TPB, 0, st>>>(P, first, n, t_start, dt, g_tuning.refill_min);
+  const int rf = g_tuning.refill_min;
+  if (P.cl.opacity_model != JB_OPAC_GRAY)
+    k_transport_imc<NDIM, MINB, VALIDATE, ABS_GENERIC><<<(unsigned)blocks, IMC_TPB, 0, st>>>(P, first, n, t_start, dt, rf);
+  else if (P.cl.gray_mode == JB_GRAY_DIRECT)
+    k_transport_imc<NDIM, MINB, VALIDATE, ABS_GRAY_DIRECT><<<(unsigned)blocks, IMC_TPB, 0, st>>>(P, first, n, t_start, dt, rf);
   else
-    k_transport_imc<NDIM, MINB, false><<<(unsigned)blocks, IMC_TPB, 0, st>>>(P, first, n, t_start, dt, g_tuning.refill_min);
+    k_transport_imc<NDIM, MINB, VALIDATE, ABS_GRAY_KIRCHHOFF><<<(unsigned)blocks, IMC_TPB, 0, st>>>(P, first, n, t_start, dt, rf);
 }
 template <int NDIM>
 static void launch_transport_imc(const StepParams &P, long long first, long long n, double t_start, double dt,
                                  cudaStream_t st) {
+  if (g_tuning.validate) {  // the cross-checked build exists for one occupancy only
+    launch_transport_imc_abs<NDIM, 4, true>(P, first, n, t_start, dt, st);
+    return;
+  }
   switch (g_tuning.ctas_per_sm) {
-    case 3: launch_transport_imc_occ<NDIM, 3>(P, first, n, t_start, dt, st); break;
-    case 5: launch_transport_imc_occ<NDIM, 5>(P, first, n, t_start, dt, st); break;
-    case 6: launch_transport_imc_occ<NDIM, 6>(P, first, n, t_start, dt, st); break;
-    case 8: launch_transport_imc_occ<NDIM, 8>(P, first, n, t_start, dt, st); break;
-    default: launch_transport_imc_occ<NDIM, 4>(P, first, n, t_start, dt, st); break;
+    case 4: launch_transport_imc_abs<NDIM, 4, false>(P, first, n, t_start, dt, st); break;
+    case 6: launch_transport_imc_abs<NDIM, 6, false>(P, first, n, t_start, dt, st); break;
+    default: launch_transport_imc_abs<NDIM, 8, false>(P, first, n, t_start, dt, st); break;
   }
 }
 

@@ -42,6 +42,9 @@
 #include <limits>
 #include <string>
 #include <vector>
+#if defined(_OPENMP)
+#include <omp.h>
+#endif
 
 #include "../include/jaybenne_b200.h"
 #include "../jaybenne_b200/csrc/jb_math.h"
@@ -95,6 +98,12 @@ struct XorShift64 {
   }
 };
 
+// one pool entry per cache line pair, so threads that each own a state do not share lines
+// (Kokkos pads its state view the same way)
+struct alignas(128) PoolState : XorShift64 {
+  explicit PoolState(uint64_t s = 1318319) : XorShift64(s) {}
+};
+
 // The generator handed to the physics functions. In PHILOX mode it is the particle's
 // stream: double #n = words (2*(n&1), 2*(n&1)+1) of Philox block n>>1 with counter
 // (n>>1, idx, gid, call) and key (seed_lo, seed_hi ^ stream); value = (u64 >> 11) * 2^-53.
@@ -105,7 +114,7 @@ struct RngGen {
   uint32_t key[2] = {0, 0};
   XorShift64 *xs = nullptr;
   double drand() {
-    if (mode == JB_RNG_XORSHIFT_POOL) return xs->drand();
+    if (mode != JB_RNG_PHILOX) return xs->drand();
     const uint32_t ctr[4] = {n >> 1, id[0], id[1], id[2]};
     uint32_t o[4];
     philox4x32_10(ctr, key, o);
@@ -663,7 +672,7 @@ struct Ctx {
   int my_rank = 0, n_ranks = 1;
   bool mesh_set = false;
   uint32_t source_call = 0;
-  std::vector<XorShift64> pool;        // reference-faithful generator pool
+  std::vector<PoolState> pool;        // reference-faithful generator pool
   std::vector<std::vector<ExRecord>> outbox;  // per peer rank
   jb_cycle_stats stats;
   std::vector<jb_event> events;
@@ -676,6 +685,17 @@ struct Ctx {
 static jb_status fail(Ctx *c, jb_status s, const std::string &m) {
   if (c) c->err = m;
   return s;
+}
+
+// which pool state the calling thread borrows: state 0 in the serial, reproducible mode; one
+// state per OpenMP thread in JB_RNG_XORSHIFT_THREADS (what Random_XorShift64_Pool hands out on
+// the Kokkos OpenMP backend, where num_states = concurrency()) — timing builds only
+static inline int pool_slot(int mode) {
+#if defined(_OPENMP)
+  if (mode == JB_RNG_XORSHIFT_THREADS) return omp_get_thread_num();
+#endif
+  (void)mode;
+  return 0;
 }
 
 // Kokkos::Random_XorShift64_Pool::init (Kokkos_Random.hpp:891-940)
@@ -692,15 +712,15 @@ static void seed_pool(Ctx *c, int num_states) {
     int n4 = gen.rand();
     uint64_t s = (((static_cast<uint64_t>(n1)) & 0xffff) << 00) | (((static_cast<uint64_t>(n2)) & 0xffff) << 16) |
                  (((static_cast<uint64_t>(n3)) & 0xffff) << 32) | (((static_cast<uint64_t>(n4)) & 0xffff) << 48);
-    c->pool.push_back(XorShift64(s));
+    c->pool.push_back(PoolState(s));
   }
 }
 
 static RngGen particle_rng(Ctx *c, const Particle &p) {
   RngGen g;
   g.mode = c->cfg.rng_mode;
-  if (g.mode == JB_RNG_XORSHIFT_POOL) {
-    g.xs = &c->pool[0];
+  if (g.mode != JB_RNG_PHILOX) {
+    g.xs = &c->pool[pool_slot(g.mode)];
     return g;
   }
   g.id[0] = p.rid[0];
@@ -714,8 +734,8 @@ static RngGen particle_rng(Ctx *c, const Particle &p) {
 static RngGen cell_rng(Ctx *c, uint32_t cell, uint32_t gid, uint32_t call) {
   RngGen g;
   g.mode = c->cfg.rng_mode;
-  if (g.mode == JB_RNG_XORSHIFT_POOL) {
-    g.xs = &c->pool[0];
+  if (g.mode != JB_RNG_PHILOX) {
+    g.xs = &c->pool[pool_slot(g.mode)];
     return g;
   }
   g.id[0] = cell;
@@ -1481,7 +1501,13 @@ jb_status jbo_create(const jb_config *cfg, jb_ctx **out) {
   c->cl.init(*cfg);
   memset(&c->stats, 0, sizeof(c->stats));
   memset(&c->mesh, 0, sizeof(c->mesh));
-  jbo::seed_pool(c, 1);
+  {
+    int states = 1;
+#if defined(_OPENMP)
+    if (cfg->rng_mode == JB_RNG_XORSHIFT_THREADS) states = omp_get_max_threads();
+#endif
+    jbo::seed_pool(c, states);
+  }
   *out = c;
   return JB_OK;
 }
