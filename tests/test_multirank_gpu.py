@@ -1,0 +1,192 @@
+"""The N > 1 path of the CUDA library.
+
+1. two rank contexts on ONE GPU, swarm exchange staged through the host (jb_exchange_take /
+   jb_exchange_give): exercises the device outbox written by the transport kernel, the unpack
+   kernel and the iteration-until-complete loop, and runs wherever one GPU is available;
+2. two processes on TWO GPUs, exchange over NCCL inside jb_radiation_step (skipped with < 2 GPUs).
+
+Random streams are keyed per photon, so in both cases the union of the ranks' swarms must equal
+the single-rank swarm bit for bit and every block's fields must agree to the atomic-order
+tolerance (1e-12) — a property the reference does not have.
+"""
+import os
+import pickle
+import socket
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+import pytest
+
+import parity_util as pu
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+FIELDS = ("energy_tally", "energy_delta", "internal_energy", "fleck_factor")
+
+
+def _build(text, rank, world, nblocks_total, capacity=0):
+    from jaybenne_b200 import Mcblock, device_api
+    return Mcblock(pu.make_pin(text=text), api=device_api(), rank=rank, n_ranks=world, capacity=capacity,
+                   cfg_overrides={"source_nblocks": nblocks_total})
+
+
+def _collect(mb, hist):
+    return {"particles": mb.jb.particles(), "history": hist,
+            "fields": {g: {n: mb.jb.get_field(g, n) for n in FIELDS} for g in mb.jb.local_gids}}
+
+
+def _single_rank(text, nblocks_total, cycles):
+    mb = _build(text, 0, 1, nblocks_total)
+    mb.ProblemGenerator(pu.synthetic_density)
+    hist = []
+    for _ in range(cycles):
+        hist.append(mb.Step())
+        mb.time += mb.dt
+    return _collect(mb, hist)
+
+
+def _compare(one, parts, cycles):
+    for c in range(cycles):
+        for k in ("n_sourced", "n_absorbed", "n_end", "n_segments", "n_scatters", "n_block_crossings"):
+            assert sum(p["history"][c][k] for p in parts) == one["history"][c][k], (c, k)
+        sent = sum(p["history"][c]["n_sent"] for p in parts)
+        assert sent == sum(p["history"][c]["n_received"] for p in parts) and sent > 0
+        e2 = sum(p["history"][c]["e_end"] for p in parts)
+        assert abs(e2 - one["history"][c]["e_end"]) <= 1e-12 * abs(e2)
+    merged = {k: np.concatenate([p["particles"][k] for p in parts]) for k in one["particles"]}
+
+    def order(p):
+        return np.lexsort((p["rng"][:, 0], p["rng"][:, 1], p["rng"][:, 2]))
+    o1, o2 = order(one["particles"]), order(merged)
+    assert len(o1) == len(o2)
+    for k in one["particles"]:
+        assert np.array_equal(one["particles"][k][o1], merged[k][o2]), k
+    seen = set()
+    for p in parts:
+        for g, f in p["fields"].items():
+            seen.add(g)
+            for name, arr in f.items():
+                ref = one["fields"][g][name]
+                scale = max(np.max(np.abs(ref)), 1e-300)
+                assert np.max(np.abs(arr - ref)) / scale <= 1e-12, (g, name)
+    assert seen == set(one["fields"])
+
+
+def _step_ranks_hosted(mbs, t, dt):
+    """radiation_step_hosted (jaybenne_b200/package.py) for several rank contexts in one process."""
+    from jaybenne_b200 import capi
+    jbs = [mb.jb for mb in mbs]
+    n = len(jbs)
+    for jb in jbs:
+        jb.stats_begin()
+        jb.UpdateDerivedTransportFields(dt)
+        jb.SourcePhotons(capi.JB_SOURCE_EMISSION, t, dt)
+    it = 0
+    while True:
+        it += 1
+        assert it < 100
+        out = []
+        for jb in jbs:
+            jb.TransportPhotons(t, dt)
+            jb.SwarmExchange()
+            out.append([jb.exchange_take(p) if p != jb.rank else b"" for p in range(n)])
+        for r, jb in enumerate(jbs):
+            for src in range(n):
+                if src != r:
+                    jb.exchange_give(out[src][r])
+        if sum(jb.CheckCompletion(t + dt) for jb in jbs) == 0:
+            break
+    stats = []
+    for mb in mbs:
+        mb.jb.EvaluateRadiationEnergy()
+        mb.jb.UpdateFluid()
+        st = mb.jb.stats()
+        st["n_iterations"] = it
+        mb.jb.UpdateDerivedMaterial()   # McblockDriver::Step's FillDerived
+        stats.append(st)
+    return stats
+
+
+@pytest.mark.parametrize("ndim,n,nb,world", [(3, 16, 8, 2), (3, 16, 4, 4), (2, 32, 8, 2)])
+def test_rank_contexts_on_one_gpu_equal_one_rank(ndim, n, nb, world):
+    # no material feedback: the second cycle's source weights would inherit the last bits of
+    # energy_delta, an atomic sum whose order differs between runs
+    text = pu.synthetic_text(n=n, nb=nb, num_particles=40000, ndim=ndim, do_feedback=False)
+    nblocks_total = (n // nb) ** ndim
+    cycles = 2
+    one = _single_rank(text, nblocks_total, cycles)
+    mbs = [_build(text, r, world, nblocks_total, capacity=60000) for r in range(world)]
+    for mb in mbs:
+        mb.ProblemGenerator(pu.synthetic_density)
+    hists = [[] for _ in mbs]
+    for _ in range(cycles):
+        sts = _step_ranks_hosted(mbs, mbs[0].time, mbs[0].dt)
+        for mb, h, st in zip(mbs, hists, sts):
+            h.append(st)
+            mb.time += mb.dt
+    _compare(one, [_collect(mb, h) for mb, h in zip(mbs, hists)], cycles)
+
+
+_WORKER = r"""
+import os, pickle, sys
+sys.path.insert(0, {root!r}); sys.path.insert(0, {here!r})
+import torch, torch.distributed as dist
+import parity_util as pu
+import test_multirank_gpu as T
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+text = open({textfile!r}).read()
+mb = T._build(text, rank, world, {nblocks_total}, capacity=200000)
+idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+if rank == 0:
+    import ctypes as C
+    raw = C.create_string_buffer(128)
+    assert mb.jb.api.comm_unique_id(raw) == 0
+    idbuf.copy_(torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8))
+dist.broadcast(idbuf, 0)
+mb.jb.comm_init(bytes(idbuf.cpu().numpy().tobytes()))
+mb.ProblemGenerator(pu.synthetic_density)
+hist = []
+for _ in range({cycles}):
+    hist.append(mb.Step())          # jb_radiation_step: NCCL exchange inside the library
+    mb.time += mb.dt
+pickle.dump(T._collect(mb, hist), open(os.path.join({outdir!r}, "rank%d.pkl" % rank), "wb"))
+dist.barrier()
+dist.destroy_process_group()
+"""
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_nccl_ranks_equal_one_rank(world):
+    import torch
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    n, nb, ndim, cycles = 32, 8, 3, 2
+    text = pu.synthetic_text(n=n, nb=nb, num_particles=200000, ndim=ndim, do_feedback=False)
+    nblocks_total = (n // nb) ** ndim
+    one = _single_rank(text, nblocks_total, cycles)
+    with tempfile.TemporaryDirectory() as d:
+        textfile = os.path.join(d, "deck.in")
+        open(textfile, "w").write(text)
+        script = os.path.join(d, "worker.py")
+        open(script, "w").write(_WORKER.format(root=ROOT, here=HERE, textfile=textfile, nblocks_total=nblocks_total,
+                                               cycles=cycles, outdir=d))
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+               "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), script]
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+        parts = [pickle.load(open(os.path.join(d, f"rank{q}.pkl"), "rb")) for q in range(world)]
+    _compare(one, parts, cycles)
