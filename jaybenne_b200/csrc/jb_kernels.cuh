@@ -116,6 +116,7 @@ struct StepParams {
   EventLog log;
   DStats *stats;
   double *ebins;  // [EB_KINDS][EBINS]
+  unsigned long long *work;  // chunk counter of the persistent transport kernel (zero at launch)
   uint32_t key0, key1_particle, key1_cell;
   int use_ddmc;
   double tau_ddmc;

@@ -215,6 +215,7 @@ static StepParams make_params(jb_ctx *c) {
   P.log.count = c->d_stats ? &c->d_stats->n_events : nullptr;
   P.stats = c->d_stats;
   P.ebins = c->d_ebins;
+  P.work = c->d_counters + 6;
   P.key0 = (uint32_t)((uint64_t)c->cfg.seed);
   P.key1_particle = (uint32_t)((uint64_t)c->cfg.seed >> 32) ^ STREAM_PARTICLE;
   P.key1_cell = (uint32_t)((uint64_t)c->cfg.seed >> 32) ^ STREAM_CELL;
@@ -830,6 +831,7 @@ static jb_status transport_range(jb_ctx *c, long long first, long long n, double
     c->launches += 1;
     c->props_dirty = false;
   }
+  JB_CUDA(c, cudaMemsetAsync(P.work, 0, sizeof(unsigned long long), c->stream));
   launch_transport(P, first, n, t_start, dt, c->stream);
   c->launches += n > 0;
   JB_CUDA(c, cudaGetLastError());

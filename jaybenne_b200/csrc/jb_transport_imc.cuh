@@ -28,6 +28,7 @@
 #define JAYBENNE_B200_JB_TRANSPORT_IMC_CUH_
 
 static constexpr int IMC_TPB = 128;
+static constexpr int IMC_CHUNK = 1024;  // slots per claim: 8 KB of each swarm array
 
 __device__ __forceinline__ CellProps load_props(const CellProps *p) {
   // 2 x 16-byte read-only loads of one 32-byte aligned record
@@ -174,12 +175,10 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
   const unsigned lane = threadIdx.x & 31u;
   const unsigned lt_mask = (1u << lane) - 1u;
   const long long gw = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
-  const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
-  // this warp's slots: a contiguous range, a multiple of 32 long so ranges start on 256 B lines
-  const long long per = (((n + nw - 1) / nw) + 31) & ~31LL;
-  long long cur = first + gw * per;
-  long long end = cur + per;
-  if (end > first + n) end = first + n;
+  // a warp works through chunks of IMC_CHUNK contiguous slots claimed from one device counter,
+  // so no warp is left with a long static range while the rest of the GPU has drained
+  long long cur = 0, end = 0;
+  bool exhausted = false;
 
   bool have = false;     // this lane holds a photon in flight
   long long idx = 0;     // its slot
@@ -204,7 +203,20 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
 
   for (;;) {
     // ---- refill idle lanes from the warp's range ----------------------------------------
-    while (cur < end) {
+    for (;;) {
+      if (cur >= end) {
+        if (exhausted) break;
+        unsigned long long c0 = 0;
+        if (lane == 0) c0 = atomicAdd(P.work, (unsigned long long)IMC_CHUNK);
+        c0 = __shfl_sync(FULL, c0, 0);
+        if ((long long)c0 >= n) {
+          exhausted = true;
+          break;
+        }
+        cur = first + (long long)c0;
+        end = cur + IMC_CHUNK;
+        if (end > first + n) end = first + n;
+      }
       const unsigned need = __ballot_sync(FULL, !have);
       const int cnt = __popc(need);
       if (cnt < refill_min && cnt < 32) break;
@@ -253,13 +265,14 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
     if (have) {
       // ---- one segment of the while (t < t_end) loop, transport.cpp:112-171 ------------
       c_seg++;
-      double xi_abs, xi_sc;
-      rng.draw2(P.key0, P.key1_particle, xi_abs, xi_sc);
+      // loads first: their latency hides behind the Philox block
+      const long long ci = (long long)lb * m.ncell + ((long long)p.kp * nx2 + p.jp) * nx1 + p.ip;
+      const CellProps cp = load_props(P.f.props + ci);
       const BlkGeo *geo = m.geo + gid;
       const double2 gx = __ldg(&geo->xd[0]), gy = __ldg(&geo->xd[1]), gz = __ldg(&geo->xd[2]);
       const double dx_cell = __ldg(&geo->dx_push);
-      const long long ci = (long long)lb * m.ncell + ((long long)p.kp * nx2 + p.jp) * nx1 + p.ip;
-      const CellProps cp = load_props(P.f.props + ci);
+      double xi_abs, xi_sc;
+      rng.draw2(P.key0, P.key1_particle, xi_abs, xi_sc);
       CellEnv c;
       {
         // coords.Xc<d>(i) -/+ dx/2 (transport.cpp:114-119), Xc as UniformCartesian computes it
