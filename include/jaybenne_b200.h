@@ -213,6 +213,11 @@ jb_status jb_set_capacity(jb_ctx *ctx, int64_t max_particles);
  * a device pointer. gid must be a block owned by this rank. */
 jb_status jb_set_field(jb_ctx *ctx, int32_t gid, int32_t field, const double *src);
 jb_status jb_get_field(jb_ctx *ctx, int32_t gid, int32_t field, double *dst_host);
+/* Multi-rank DDMC: density / sie of a block owned by ANOTHER rank (the ghost-zone exchange of
+ * src/mcblock/mcblock_driver.cpp:68 + jaybenne.cpp:108-110 as one whole-block copy). Needed
+ * before jb_update_derived_transport_fields only when the host program moves the data itself;
+ * with jb_comm_init the library exchanges the blocks over NCCL. No-op on one rank / without DDMC. */
+jb_status jb_set_remote_field(jb_ctx *ctx, int32_t gid, int32_t field, const double *src);
 /* number of values of `field` per block */
 int64_t jb_field_size(const jb_ctx *ctx, int32_t field);
 

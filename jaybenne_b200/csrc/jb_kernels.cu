@@ -148,12 +148,20 @@ __device__ double sample_cell_leaf(const StepParams &P, int field, int L, const 
   const int gid = lattice_at(m, l[0], l[1], l[2]);
   const DBlock &nb = m.blocks[gid];
   finer = false;
-  if (nb.local < 0) return jbm::mk_nan();
-  const double *f = field == 0 ? P.f.rho : P.f.sie;
+  const double *f;
+  size_t blk;
+  if (P.f.g_rho) {  // multi-rank: the mirror of all blocks, indexed by gid
+    f = field == 0 ? P.f.g_rho : P.f.g_sie;
+    blk = (size_t)gid;
+  } else {
+    if (nb.local < 0) return jbm::mk_nan();
+    f = field == 0 ? P.f.rho : P.f.sie;
+    blk = (size_t)nb.local;
+  }
   if (nb.level <= L) {
     int idx[3] = {0, 0, 0};
     for (int d = 0; d < m.ndim; ++d) idx[d] = (int)((G[d] >> (L - nb.level)) - (long long)nb.lx[d] * m.nxb[d]);
-    return f[(size_t)nb.local * m.ncell + ((size_t)idx[2] * m.nxb[1] + idx[1]) * m.nxb[0] + idx[0]];
+    return f[blk * m.ncell + ((size_t)idx[2] * m.nxb[1] + idx[1]) * m.nxb[0] + idx[0]];
   }
   finer = true;
   return 0.0;

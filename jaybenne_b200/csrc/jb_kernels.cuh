@@ -60,6 +60,10 @@ struct __align__(32) CellProps {
 struct Fields {
   double *rho, *sie, *u, *tally, *fleck, *src_ew, *src_num, *edelta;
   CellProps *props;
+  // multi-rank DDMC only: rho and sie of EVERY block, [gid][cell], so the face probabilities at a
+  // rank boundary see the neighbour's cells (the reference exchanges ghost zones, jaybenne.cpp:108-110
+  // and mcblock_driver.cpp:68); null when one rank owns the whole mesh
+  double *g_rho, *g_sie;
   double *fp[3];
   long long nface[3];  // values per block of fp[d]
 };

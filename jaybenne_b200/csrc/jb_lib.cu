@@ -335,7 +335,7 @@ void jb_destroy(jb_ctx *c) {
   free_swarm(c);
   dfree(c->d_blocks); dfree(c->d_lattice); dfree(c->d_local_gid); dfree(c->d_nbr); dfree(c->d_geo);
   dfree(c->f.rho); dfree(c->f.sie); dfree(c->f.u); dfree(c->f.tally); dfree(c->f.fleck);
-  dfree(c->f.src_ew); dfree(c->f.src_num); dfree(c->f.edelta);
+  dfree(c->f.src_ew); dfree(c->f.src_num); dfree(c->f.edelta); dfree(c->f.g_rho); dfree(c->f.g_sie);
   for (int d = 0; d < 3; ++d) dfree(c->f.fp[d]);
   dfree(c->d_cnt); dfree(c->d_prefix); dfree(c->d_scan); dfree(c->d_total);
   dfree(c->d_holes); dfree(c->d_tails); dfree(c->d_counters); dfree(c->d_esum); dfree(c->d_stats);
@@ -488,6 +488,12 @@ jb_status jb_set_mesh(jb_ctx *c, const jb_mesh *m, int32_t my_rank, int32_t n_ra
   c->f.nface[0] = (long long)(m->nxb[0] + 1) * m->nxb[1] * m->nxb[2];
   c->f.nface[1] = (long long)m->nxb[0] * (m->nxb[1] + 1) * m->nxb[2];
   c->f.nface[2] = (long long)m->nxb[0] * m->nxb[1] * (m->nxb[2] + 1);
+  if (c->cfg.use_ddmc && n_ranks > 1) {
+    JB_CUDA(c, dalloc(&c->f.g_rho, nc * m->nblocks));
+    JB_CUDA(c, dalloc(&c->f.g_sie, nc * m->nblocks));
+    JB_CUDA(c, cudaMemset(c->f.g_rho, 0, sizeof(double) * (size_t)(nc * m->nblocks)));
+    JB_CUDA(c, cudaMemset(c->f.g_sie, 0, sizeof(double) * (size_t)(nc * m->nblocks)));
+  }
   if (c->cfg.use_ddmc) {
     for (int d = 0; d < 3; ++d) {
       JB_CUDA(c, dalloc(&c->f.fp[d], c->f.nface[d] * nl));
@@ -539,6 +545,20 @@ jb_status jb_set_field(jb_ctx *c, int32_t gid, int32_t field, const double *src)
   JB_CUDA(c, cudaMemcpyAsync(p + (size_t)c->gid_to_local[gid] * nb, src, sizeof(double) * nb, cudaMemcpyDefault, c->stream));
   JB_CUDA(c, cudaStreamSynchronize(c->stream));
   c->props_dirty = true;
+  return JB_OK;
+}
+// rho / sie of a block another rank owns, for hosts that move the DDMC ghost data themselves
+jb_status jb_set_remote_field(jb_ctx *c, int32_t gid, int32_t field, const double *src) {
+  if (!c || !src) return JB_ERR_INVALID;
+  if (!c->mesh_set) return fail(c, JB_ERR_STATE, "mesh not set");
+  if (gid < 0 || gid >= c->mesh.nblocks) return fail(c, JB_ERR_INVALID, "bad block");
+  if (field != JB_FIELD_DENSITY && field != JB_FIELD_SIE) return fail(c, JB_ERR_INVALID, "remote fields are density and sie");
+  if (!c->f.g_rho) return JB_OK;  // nothing reads them (single rank or no DDMC)
+  const long long nc = (long long)c->mesh.nxb[0] * c->mesh.nxb[1] * c->mesh.nxb[2];
+  double *dst = (field == JB_FIELD_DENSITY ? c->f.g_rho : c->f.g_sie) + (size_t)gid * nc;
+  JB_CUDA(c, cudaSetDevice(c->device));
+  JB_CUDA(c, cudaMemcpyAsync(dst, src, sizeof(double) * nc, cudaMemcpyDefault, c->stream));
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
   return JB_OK;
 }
 jb_status jb_get_field(jb_ctx *c, int32_t gid, int32_t field, double *dst) {
@@ -763,6 +783,46 @@ static jb_status sort_by_cell(jb_ctx *c) {
   return JB_OK;
 }
 
+// Multi-rank DDMC: bring the mirror of every block's rho and sie up to date. Own blocks are
+// copied in; with an NCCL communicator every rank sends its blocks to every peer (grouped
+// send/recv, one exchange per cycle like the reference's ghost exchange); without one the host
+// program is expected to have delivered the other ranks' blocks through jb_set_remote_field.
+static jb_status refresh_field_mirror(jb_ctx *c) {
+  const long long nc = (long long)c->mesh.nxb[0] * c->mesh.nxb[1] * c->mesh.nxb[2];
+  for (size_t q = 0; q < c->local_gid.size(); ++q) {
+    const size_t g = (size_t)c->local_gid[q];
+    JB_CUDA(c, cudaMemcpyAsync(c->f.g_rho + g * nc, c->f.rho + q * nc, sizeof(double) * nc, cudaMemcpyDeviceToDevice, c->stream));
+    JB_CUDA(c, cudaMemcpyAsync(c->f.g_sie + g * nc, c->f.sie + q * nc, sizeof(double) * nc, cudaMemcpyDeviceToDevice, c->stream));
+  }
+  if (!c->comm) return JB_OK;
+  NcclApi &nc_api = nccl_api();
+  if (!nc_api.ok) return fail(c, JB_ERR_COMM, "NCCL is not available");
+  // blocks are owned in runs of consecutive gids: send / receive run by run
+  bool err = nc_api.GroupStart() != ncclSuccess;
+  const int nb = c->mesh.nblocks;
+  int g = 0;
+  while (g < nb && !err) {
+    const int owner = c->all_blocks[g].rank;
+    int e = g;
+    while (e < nb && c->all_blocks[e].rank == owner) ++e;
+    const size_t off = (size_t)g * nc, cnt = (size_t)(e - g) * nc;
+    if (owner == c->my_rank) {
+      for (int peer = 0; peer < c->n_ranks && !err; ++peer) {
+        if (peer == c->my_rank) continue;
+        err |= nc_api.Send(c->f.g_rho + off, cnt, ncclDouble, peer, c->comm, c->stream) != ncclSuccess;
+        err |= nc_api.Send(c->f.g_sie + off, cnt, ncclDouble, peer, c->comm, c->stream) != ncclSuccess;
+      }
+    } else {
+      err |= nc_api.Recv(c->f.g_rho + off, cnt, ncclDouble, owner, c->comm, c->stream) != ncclSuccess;
+      err |= nc_api.Recv(c->f.g_sie + off, cnt, ncclDouble, owner, c->comm, c->stream) != ncclSuccess;
+    }
+    g = e;
+  }
+  err |= nc_api.GroupEnd() != ncclSuccess;
+  if (err) return fail(c, JB_ERR_COMM, "DDMC ghost exchange (rho, sie) over NCCL failed");
+  return JB_OK;
+}
+
 #define JB_REQUIRE_MESH(c)                                          \
   do {                                                              \
     if (!(c)) return JB_ERR_INVALID;                                \
@@ -778,8 +838,10 @@ jb_status jb_update_derived_transport_fields(jb_ctx *c, double dt) {
   c->launches += 1;
   c->props_dirty = true;
   if (c->cfg.use_ddmc) {
-    if ((int)c->local_gid.size() != c->mesh.nblocks)
-      return fail(c, JB_ERR_UNSUPPORTED, "DDMC face probabilities need every block on one rank (no ghost exchange yet)");
+    if (c->f.g_rho) {
+      jb_status s = refresh_field_mirror(c);
+      if (s != JB_OK) return s;
+    }
     launch_face_prob(P, c->stream);
     c->launches += c->mesh.ndim;
   }

@@ -104,6 +104,11 @@ class Jaybenne:
         """`ptr`: raw host or device address of field_size(name) doubles."""
         self._check(self.api.set_field(self._ctx, gid, FIELDS[name], C.c_void_p(ptr)))
 
+    def set_remote_field(self, gid, name, values):
+        """density / sie of a block another rank owns (multi-rank DDMC, host-driven exchange)."""
+        a = np.ascontiguousarray(values, dtype=np.float64).ravel()
+        self._check(self.api.set_remote_field(self._ctx, gid, FIELDS[name], a.ctypes.data_as(C.c_void_p)))
+
     def get_field(self, gid, name, out=None):
         a = out if out is not None else np.empty(self.field_size(name), dtype=np.float64)
         self._check(self.api.get_field(self._ctx, gid, FIELDS[name], a.ctypes.data_as(C.c_void_p)))
@@ -252,7 +257,8 @@ EVENT_DTYPE = np.dtype([
 assert EVENT_DTYPE.itemsize == C.sizeof(jb_event)
 
 
-def radiation_step_hosted(jb: Jaybenne, t_start: float, dt: float, all_to_all, all_reduce_sum) -> dict:
+def radiation_step_hosted(jb: Jaybenne, t_start: float, dt: float, all_to_all, all_reduce_sum,
+                          all_gather_fields=None) -> dict:
     """RadiationStep with the swarm exchange driven from the host (jaybenne.cpp:104-138).
 
     For transports other than the library's own NCCL path (and for the CPU tests, which run
@@ -260,6 +266,14 @@ def radiation_step_hosted(jb: Jaybenne, t_start: float, dt: float, all_to_all, a
     `all_reduce_sum(int) -> int` are supplied by the caller.
     """
     jb.stats_begin()
+    if jb.cfg.use_ddmc and jb.n_ranks > 1 and all_gather_fields is not None:
+        # the ghost exchange of density / sie that precedes the face probabilities
+        # (mcblock_driver.cpp:68, jaybenne.cpp:108-110): whole blocks, every rank gets every block
+        mine = {g: (jb.get_field(g, "density"), jb.get_field(g, "sie")) for g in jb.local_gids}
+        for g, (rho, sie) in all_gather_fields(mine).items():
+            if g not in mine:
+                jb.set_remote_field(g, "density", rho)
+                jb.set_remote_field(g, "sie", sie)
     jb.UpdateDerivedTransportFields(dt)
     jb.SourcePhotons(JB_SOURCE_EMISSION, t_start, dt)
     it = 0

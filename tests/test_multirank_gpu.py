@@ -49,9 +49,9 @@ def _single_rank(text, nblocks_total, cycles):
     return _collect(mb, hist)
 
 
-def _compare(one, parts, cycles):
+def _compare(one, parts, cycles, extra_counts=()):
     for c in range(cycles):
-        for k in ("n_sourced", "n_absorbed", "n_end", "n_segments", "n_scatters", "n_block_crossings"):
+        for k in ("n_sourced", "n_absorbed", "n_end", "n_segments", "n_scatters", "n_block_crossings") + tuple(extra_counts):
             assert sum(p["history"][c][k] for p in parts) == one["history"][c][k], (c, k)
         sent = sum(p["history"][c]["n_sent"] for p in parts)
         assert sent == sum(p["history"][c]["n_received"] for p in parts) and sent > 0
@@ -81,6 +81,13 @@ def _step_ranks_hosted(mbs, t, dt):
     from jaybenne_b200 import capi
     jbs = [mb.jb for mb in mbs]
     n = len(jbs)
+    if jbs[0].cfg.use_ddmc:   # ghost exchange of density / sie ahead of the face probabilities
+        owned = {g: (jb.get_field(g, "density"), jb.get_field(g, "sie")) for jb in jbs for g in jb.local_gids}
+        for jb in jbs:
+            for g, (rho, sie) in owned.items():
+                if g not in jb.local_gids:
+                    jb.set_remote_field(g, "density", rho)
+                    jb.set_remote_field(g, "sie", sie)
     for jb in jbs:
         jb.stats_begin()
         jb.UpdateDerivedTransportFields(dt)
@@ -98,6 +105,8 @@ def _step_ranks_hosted(mbs, t, dt):
             for src in range(n):
                 if src != r:
                     jb.exchange_give(out[src][r])
+            if jb.cfg.use_ddmc:
+                jb.SampleDDMCBlockFace()
         if sum(jb.CheckCompletion(t + dt) for jb in jbs) == 0:
             break
     stats = []
@@ -131,6 +140,47 @@ def test_rank_contexts_on_one_gpu_equal_one_rank(ndim, n, nb, world):
     _compare(one, [_collect(mb, h) for mb, h in zip(mbs, hists)], cycles)
 
 
+@pytest.mark.parametrize("deck,world", [("stepdiff_smr_ddmc", 2), ("stepdiff_smr_hybrid", 4), ("stepdiff_ddmc", 2)])
+def test_ddmc_rank_contexts_on_one_gpu_equal_one_rank(deck, world):
+    """Multi-rank DDMC / hybrid on the static-refinement decks: face probabilities at rank
+    boundaries come from the neighbour rank's density / sie (jb_set_remote_field), photons that
+    change rank are re-sampled on the block face after they arrive."""
+    from jaybenne_b200 import Mcblock, device_api
+    ci = deck != "stepdiff_smr_hybrid"          # the hybrid deck at shipped resolution is the true hybrid
+    ov = [("jaybenne", "num_particles", 20000)]
+    if deck == "stepdiff_ddmc":
+        ov.append(("parthenon/meshblock", "nx1", 32))   # CI runs one 128-cell block: split it in four
+    cycles = 2
+
+    def build(rank, n_ranks):
+        return Mcblock(pu.make_pin(deck, overrides=ov, ci=ci), api=device_api(), rank=rank, n_ranks=n_ranks,
+                       capacity=40000)
+    one_mb = build(0, 1)
+    one_mb.ProblemGenerator()
+    h1 = []
+    for _ in range(cycles):
+        h1.append(one_mb.Step())
+        one_mb.time += one_mb.dt
+    one = _collect(one_mb, h1)
+    assert h1[-1]["n_ddmc_segments"] > 0
+    mbs = [build(r, world) for r in range(world)]
+    for mb in mbs:
+        mb.ProblemGenerator()
+    hists = [[] for _ in mbs]
+    for _ in range(cycles):
+        sts = _step_ranks_hosted(mbs, mbs[0].time, mbs[0].dt)
+        for mb, h, st in zip(mbs, hists, sts):
+            h.append(st)
+            mb.time += mb.dt
+    _compare(one, [_collect(mb, h) for mb, h in zip(mbs, hists)], cycles, extra_counts=("n_ddmc_segments",))
+    ndim = one_mb.mesh.c.ndim
+    for mb in mbs:   # face probabilities are deterministic: bit-identical to the one-rank values
+        for g in mb.jb.local_gids:
+            for d in range(ndim):
+                name = "ddmc_face_prob_x%d" % (d + 1)
+                assert np.array_equal(mb.jb.get_field(g, name), one_mb.jb.get_field(g, name)), (g, name)
+
+
 _WORKER = r"""
 import os, pickle, sys
 sys.path.insert(0, {root!r}); sys.path.insert(0, {here!r})
@@ -140,8 +190,13 @@ import test_multirank_gpu as T
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
 dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
-text = open({textfile!r}).read()
-mb = T._build(text, rank, world, {nblocks_total}, capacity=200000)
+deck = {deck!r}
+if deck:
+    from jaybenne_b200 import Mcblock, device_api
+    mb = Mcblock(pu.make_pin(deck, overrides={ov!r}, ci=True), api=device_api(), rank=rank, n_ranks=world,
+                 capacity=200000)
+else:
+    mb = T._build(open({textfile!r}).read(), rank, world, {nblocks_total}, capacity=200000)
 idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
 if rank == 0:
     import ctypes as C
@@ -150,7 +205,7 @@ if rank == 0:
     idbuf.copy_(torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8))
 dist.broadcast(idbuf, 0)
 mb.jb.comm_init(bytes(idbuf.cpu().numpy().tobytes()))
-mb.ProblemGenerator(pu.synthetic_density)
+mb.ProblemGenerator(None if deck else pu.synthetic_density)
 hist = []
 for _ in range({cycles}):
     hist.append(mb.Step())          # jb_radiation_step: NCCL exchange inside the library
@@ -183,10 +238,38 @@ def test_nccl_ranks_equal_one_rank(world):
         open(textfile, "w").write(text)
         script = os.path.join(d, "worker.py")
         open(script, "w").write(_WORKER.format(root=ROOT, here=HERE, textfile=textfile, nblocks_total=nblocks_total,
-                                               cycles=cycles, outdir=d))
+                                               cycles=cycles, outdir=d, deck=None, ov=None))
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
                "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), script]
         r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
         parts = [pickle.load(open(os.path.join(d, f"rank{q}.pkl"), "rb")) for q in range(world)]
     _compare(one, parts, cycles)
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_nccl_ddmc_ranks_equal_one_rank(world):
+    """stepdiff_smr_ddmc over NCCL: the density / sie ghost exchange and the photon exchange both
+    run inside jb_radiation_step."""
+    import torch
+    from jaybenne_b200 import Mcblock, device_api
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    deck, ov, cycles = "stepdiff_smr_ddmc", [("jaybenne", "num_particles", 50000)], 2
+    one_mb = Mcblock(pu.make_pin(deck, overrides=ov, ci=True), api=device_api())
+    one_mb.ProblemGenerator()
+    h1 = []
+    for _ in range(cycles):
+        h1.append(one_mb.Step())
+        one_mb.time += one_mb.dt
+    one = _collect(one_mb, h1)
+    with tempfile.TemporaryDirectory() as d:
+        script = os.path.join(d, "worker.py")
+        open(script, "w").write(_WORKER.format(root=ROOT, here=HERE, textfile="", nblocks_total=0, cycles=cycles,
+                                               outdir=d, deck=deck, ov=ov))
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+               "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), script]
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+        parts = [pickle.load(open(os.path.join(d, f"rank{q}.pkl"), "rb")) for q in range(world)]
+    _compare(one, parts, cycles, extra_counts=("n_ddmc_segments",))
