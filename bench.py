@@ -38,7 +38,7 @@ C_LIGHT = 2.99792458e10
 SEED = 349857
 
 
-def workload_text(cells, nb, particles):
+def workload_text(cells, nb, particles, stream=False):
     from jaybenne_b200 import uniform_deck_text
     delta = 1.0 / cells
     t = uniform_deck_text([cells] * 3, [nb] * 3)
@@ -49,15 +49,15 @@ integrator = rk1
 tlim = 1.0
 <jaybenne>
 num_particles = {particles}
-dt = {4 * delta / C_LIGHT!r}
+dt = {(0.5 if stream else 4.0) * delta / C_LIGHT!r}
 seed = {SEED}
 do_emission = true
 do_feedback = true
 <mcblock>
 opacity_model = constant
-opacity_constant_value = {0.1 / delta!r}
+opacity_constant_value = {0.0 if stream else 0.1 / delta!r}
 scattering_model = constant
-scattering_constant_value = {0.5 / delta!r}
+scattering_constant_value = {0.0 if stream else 0.5 / delta!r}
 initial_density = 1.0
 initial_temperature = 1.0
 initial_radiation = thermal
@@ -188,6 +188,9 @@ def main():
     ap.add_argument("--particles", type=int, default=0, help="photons per step (default 59.6 per cell -> 1e9 at 256^3)")
     ap.add_argument("--sort-interval", type=int, default=0)
     ap.add_argument("--gray-direct", action="store_true", help="sigma_a = rho*kappa instead of the reference's B_nu round trip")
+    ap.add_argument("--stream", action="store_true",
+                    help="C5-stream variant (SURVEY 8d): dt = dx/(2c), no opacity -> ~1.4 segments per photon, the "
+                         "bandwidth-bound limit of the same kernels (not the BASELINE metric's config)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-cells", type=int, default=64)
@@ -200,6 +203,9 @@ def main():
     particles = args.particles or int(round(1.0e9 * (cells / 256.0) ** 3))
     workload = (f"C5 synthetic 3D gray IMC: {cells}^3 cells, {nb}^3-cell meshblocks, periodic, {particles} thermal "
                 f"photons sourced + one full cycle per step (dt = 4dx/c, kappa*dx = 0.1, sigma*dx = 0.5)")
+    if args.stream:
+        workload = workload.replace("C5 synthetic", "C5-stream synthetic").replace(
+            "(dt = 4dx/c, kappa*dx = 0.1, sigma*dx = 0.5)", "(dt = dx/(2c), kappa = sigma = 0: free streaming)")
     config = {"workload": workload, "cells": cells, "meshblock": nb, "photons_per_step": particles,
               "parallelism": f"meshblocks over {world} rank(s), Z-order chunks", "l2": "inputs_exceed_l2",
               "gray_absorption": "direct" if args.gray_direct else "kirchhoff (reference arithmetic)",
@@ -235,7 +241,7 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    pin = ParameterInput(text=workload_text(cells, nb, particles))
+    pin = ParameterInput(text=workload_text(cells, nb, particles, args.stream))
     nblocks_total = (cells // nb) ** 3
     over = {"source_nblocks": nblocks_total, "sort_interval": args.sort_interval,
             "gray_mode": capi.JB_GRAY_DIRECT if args.gray_direct else capi.JB_GRAY_KIRCHHOFF}
