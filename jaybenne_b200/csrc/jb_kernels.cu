@@ -1010,25 +1010,40 @@ void launch_census(const StepParams &P, long long n, double t_end, unsigned long
 // ---------------------------------------------------------------------------------------
 __global__ void k_compact_find(StepParams P, long long n, long long n_alive, long long *holes, long long *tails,
                                unsigned long long *counters) {
-  // one atomic per warp and list: lanes rank themselves inside the ballot
+  // a warp scans 8 x 32 consecutive slots per step and claims list space with ONE atomic per list:
+  // every atomic hits the same two addresses, so their number (not the bytes) sets the pace
+  constexpr int ROUNDS = 8;
   const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long base = blockIdx.x * (long long)blockDim.x + (threadIdx.x & ~31u); base < n; base += stride) {
-    const long long idx = base + lane;
-    const bool valid = idx < n;
-    const bool alive = valid && P.s.loc[idx].x >= 0;
-    const bool is_hole = valid && idx < n_alive && !alive;
-    const bool is_tail = valid && idx >= n_alive && alive;
-    const unsigned mh = __ballot_sync(0xffffffffu, is_hole), mt = __ballot_sync(0xffffffffu, is_tail);
+  const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long base = warp * (32 * ROUNDS); base < n; base += nwarps * (32 * ROUNDS)) {
+    unsigned mh[ROUNDS], mt[ROUNDS];
+    int nh = 0, nt = 0;
+#pragma unroll
+    for (int r = 0; r < ROUNDS; ++r) {
+      const long long idx = base + r * 32 + lane;
+      const bool valid = idx < n;
+      const bool alive = valid && P.s.loc[idx].x >= 0;
+      mh[r] = __ballot_sync(0xffffffffu, valid && idx < n_alive && !alive);
+      mt[r] = __ballot_sync(0xffffffffu, valid && idx >= n_alive && alive);
+      nh += __popc(mh[r]);
+      nt += __popc(mt[r]);
+    }
     unsigned long long bh = 0, bt = 0;
     if (lane == 0) {
-      if (mh) bh = atomicAdd(&counters[0], (unsigned long long)__popc(mh));
-      if (mt) bt = atomicAdd(&counters[1], (unsigned long long)__popc(mt));
+      if (nh) bh = atomicAdd(&counters[0], (unsigned long long)nh);
+      if (nt) bt = atomicAdd(&counters[1], (unsigned long long)nt);
     }
     bh = __shfl_sync(0xffffffffu, bh, 0);
     bt = __shfl_sync(0xffffffffu, bt, 0);
-    if (is_hole) holes[bh + __popc(mh & lt)] = idx;
-    if (is_tail) tails[bt + __popc(mt & lt)] = idx;
+#pragma unroll
+    for (int r = 0; r < ROUNDS; ++r) {
+      const long long idx = base + r * 32 + lane;
+      if ((mh[r] >> lane) & 1u) holes[bh + __popc(mh[r] & lt)] = idx;
+      if ((mt[r] >> lane) & 1u) tails[bt + __popc(mt[r] & lt)] = idx;
+      bh += __popc(mh[r]);
+      bt += __popc(mt[r]);
+    }
   }
 }
 __global__ void k_compact_move(StepParams P, const long long *holes, const long long *tails,
