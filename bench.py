@@ -369,8 +369,21 @@ def main():
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = tr_bytes / (tr_ms * 1e-3) / 1e9 if tr_ms > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": "k_transport", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None,
+    # DRAM traffic of the kernel: measured once with ncu on the 64^3 twin (profiles/r01_traffic.json) as a ratio to
+    # the algorithmic bytes of that launch; reported here scaled to this run's launch (None if the file is absent)
+    traffic, traffic_src, ncu_pipe = None, None, {}
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        if not args.stream:
+            traffic = tj["ratio"] * tr_bytes / max(args.steps, 1)
+            traffic_src = f"ncu at {tj['cells']}^3: dram bytes / algorithmic bytes = {tj['ratio']}, scaled to this launch"
+            ncu_pipe = {"fp64_pipe_pct": tj.get("fp64_pipe_pct"), "issue_active_pct": tj.get("issue_active_pct")}
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": "k_transport_imc", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "ncu": ncu_pipe,
+                "note": "8.3 segments per photon make this kernel FP64-issue bound (~220 FP64 ops per segment against "
+                        "~17 algorithmic bytes); bench.py --stream measures the same kernel in the bandwidth-bound regime",
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
                 "bytes_per_launch": tr_bytes / max(args.steps, 1), "ms_per_launch": tr_ms / max(args.steps, 1),
                 "bytes_per_segment": tr_bytes / max(seg, 1),

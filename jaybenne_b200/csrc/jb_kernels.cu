@@ -378,7 +378,7 @@ void launch_exclusive_scan(const int *cnt, long long *prefix, long long n, long 
 // cell's new photons so the SoA stores coalesce. Photon `np` (its index in the block's
 // prefix order) keys its random stream, so the result does not depend on the schedule.
 // ---------------------------------------------------------------------------------------
-__global__ void k_source_emit(StepParams P, int first_local, long long ncells, int source_type, double t_start,
+__global__ void __launch_bounds__(256, 4) k_source_emit(StepParams P, int first_local, long long ncells, int source_type, double t_start,
                               double dt, uint32_t call, const long long *prefix, long long slot0) {
   const DMesh &m = P.mesh;
   const double vv = P.cl.c_code, sb = P.cl.sb_code;

@@ -207,3 +207,52 @@ def test_large_run_conservation_and_count_identities():
         assert abs(tally - st["e_end"]) <= 1e-11 * st["e_end"]
         edelta = sum(mb.jb.get_field(g, "energy_delta").sum() for g in mb.jb.local_gids)
         assert abs(edelta - (st["e_absorbed"] - st["e_sourced"])) <= 1e-9 * st["e_absorbed"]
+
+
+# ---- north_star check 3: seed ensembles against the reference-faithful generator ------------------
+def _ensemble(api, rng_mode, deck, overrides, cycles, seeds, ci=False):
+    from jaybenne_b200 import Mcblock
+    tallies, sies = [], []
+    for seed in seeds:
+        pin = pu.make_pin(deck, overrides=list(overrides) + [("jaybenne", "seed", seed)], ci=ci)
+        mb = Mcblock(pin, api=api, cfg_overrides={"rng_mode": rng_mode})
+        mb.ProblemGenerator()
+        for _ in range(cycles):
+            mb.Step()
+            mb.time += mb.dt
+        d = mb.dump()
+        tallies.append(np.concatenate([t.ravel() for t in d["energy_tally"]]))
+        sies.append(np.concatenate([t.ravel() for t in d["sie"]]))
+    return np.array(tallies), np.array(sies)
+
+
+def _assert_within_3_sigma(a, b, label):
+    """a, b: [seed][bin]. Means agree within 3 standard errors; with tens of bins one excursion
+    up to 4.5 sigma is allowed (p(3 sigma) = 0.27 % per bin)."""
+    se = np.sqrt(a.var(axis=0, ddof=1) / a.shape[0] + b.var(axis=0, ddof=1) / b.shape[0])
+    se = np.maximum(se, 1e-12 * np.maximum(np.abs(a.mean(axis=0)), np.abs(b.mean(axis=0))))
+    live = se > 0
+    z = np.abs(a.mean(axis=0) - b.mean(axis=0))[live] / se[live]
+    assert (z > 3.0).sum() <= 1 and z.max() <= 4.5, (label, np.sort(z)[-3:])
+
+
+def test_seed_ensemble_profiles_match_reference_generator_within_3_sigma():
+    """stepdiff (radiation profile of the Marshak wave) and inf (equilibration with feedback):
+    CUDA path with per-photon Philox streams vs the CPU oracle running the reference's
+    XorShift64 pool in serial order, 16 seeds each; T_rad ~ tally^(1/4) and T_mat ~ sie profiles
+    must agree within 3 sigma of the Monte Carlo noise."""
+    from jaybenne_b200 import capi, device_api
+    from oracle_binding import oracle_api
+    seeds = [349857 + k for k in range(16)]
+    ov = [("jaybenne", "num_particles", 4000)]
+    g_t, _ = _ensemble(device_api(), capi.JB_RNG_PHILOX, "stepdiff", ov, 3, seeds, ci=True)
+    o_t, _ = _ensemble(oracle_api("std"), capi.JB_RNG_XORSHIFT_POOL, "stepdiff", ov, 3, seeds, ci=True)
+    nb = 16                                     # 128 cells -> 16 bins of 8 cells
+    g_b = g_t.reshape(len(seeds), nb, -1).sum(axis=2)
+    o_b = o_t.reshape(len(seeds), nb, -1).sum(axis=2)
+    _assert_within_3_sigma(g_b, o_b, "stepdiff energy_tally")
+    ov = [("jaybenne", "num_particles", 200), ("jaybenne", "do_feedback", "true")]
+    g_t, g_s = _ensemble(device_api(), capi.JB_RNG_PHILOX, "inf", ov, 3, seeds)
+    o_t, o_s = _ensemble(oracle_api("std"), capi.JB_RNG_XORSHIFT_POOL, "inf", ov, 3, seeds)
+    _assert_within_3_sigma(g_t.sum(axis=1, keepdims=True), o_t.sum(axis=1, keepdims=True), "inf radiation energy")
+    _assert_within_3_sigma(g_s.mean(axis=1, keepdims=True), o_s.mean(axis=1, keepdims=True), "inf material sie")
