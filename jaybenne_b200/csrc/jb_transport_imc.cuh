@@ -448,6 +448,7 @@ static void launch_transport_imc(const StepParams &P, long long first, long long
   switch (g_tuning.ctas_per_sm) {
     case 4: launch_transport_imc_abs<NDIM, 4, false>(P, first, n, t_start, dt, st); break;
     case 6: launch_transport_imc_abs<NDIM, 6, false>(P, first, n, t_start, dt, st); break;
+    case 7: launch_transport_imc_abs<NDIM, 7, false>(P, first, n, t_start, dt, st); break;
     default: launch_transport_imc_abs<NDIM, 8, false>(P, first, n, t_start, dt, st); break;
   }
 }
