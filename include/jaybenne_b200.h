@@ -200,6 +200,11 @@ jb_status jb_create(const jb_config *cfg, jb_ctx **out);
 void jb_destroy(jb_ctx *ctx);
 const char *jb_last_error(const jb_ctx *ctx);
 int jb_abi_version(void);
+/* device selection for hosts that do not link the CUDA runtime themselves (one rank per
+ * GPU: jb_set_device(LOCAL_RANK) before jb_create). Parthenon/Kokkos does this in
+ * Kokkos::initialize (src/mcblock/main.cpp:27-35 via ParthenonManager::ParthenonInitEnv). */
+jb_status jb_device_count(int32_t *n_devices);
+jb_status jb_set_device(int32_t ordinal);
 /* speed_of_light / stefan_boltzmann Params in code units (jaybenne.cpp:181-184) */
 jb_status jb_get_constants(const jb_ctx *ctx, double *speed_of_light, double *stefan_boltzmann);
 
@@ -257,6 +262,10 @@ jb_status jb_timer_start(jb_ctx *ctx);
 jb_status jb_timer_stop(jb_ctx *ctx, double *ms);
 /* CUDA kernels launched by this context since jb_create (diagnostics / bench.py) */
 int64_t jb_kernel_launches(const jb_ctx *ctx);
+/* measurement helper (bench.py): sustained FP64 FMA rate of this GPU in TFLOP/s (2 flops per
+ * DFMA), from a register-resident chain kernel timed with CUDA events on the context's
+ * stream. It is the denominator of the FP64-pipe fraction reported beside the HBM roofline. */
+jb_status jb_measure_fp64_peak(jb_ctx *ctx, double *tflops);
 
 /* ---- event log (parity / debugging) --------------------------------------------------- */
 jb_status jb_event_log_enable(jb_ctx *ctx, int64_t capacity); /* 0 disables */

@@ -150,6 +150,9 @@ DEVICE_API = {
     "config_default": (None, [C.POINTER(jb_config)]),
     "abi_version": (C.c_int, []),
     "kernel_launches": (C.c_int64, [ctx_p]),
+    "device_count": (C.c_int, [C.POINTER(C.c_int32)]),
+    "set_device": (C.c_int, [C.c_int32]),
+    "measure_fp64_peak": (C.c_int, [ctx_p, _pd]),
     "timer_start": (C.c_int, [ctx_p]),
     "timer_stop": (C.c_int, [ctx_p, _pd]),
     "comm_unique_id": (C.c_int, [C.c_void_p]),

@@ -1155,3 +1155,24 @@ void launch_gather_b64(const void *src, void *dst, const unsigned int *perm, lon
 }
 
 }  // namespace jbd
+
+namespace jbd {
+// ---------------------------------------------------------------------------------------
+// FP64 FMA rate probe (jb_measure_fp64_peak): 8 independent register-resident DFMA chains
+// per thread, 256 threads, enough CTAs to fill every SM. 16 flops per inner iteration.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_fp64_chain(double *sink, int iters) {
+  const double a = 1.0 + 1e-9 * threadIdx.x, b = 1e-12 * (blockIdx.x + 1);
+  double r0 = 0.1, r1 = 0.2, r2 = 0.3, r3 = 0.4, r4 = 0.5, r5 = 0.6, r6 = 0.7, r7 = 0.8;
+#pragma unroll 4
+  for (int i = 0; i < iters; ++i) {
+    r0 = fma(r0, a, b); r1 = fma(r1, a, b); r2 = fma(r2, a, b); r3 = fma(r3, a, b);
+    r4 = fma(r4, a, b); r5 = fma(r5, a, b); r6 = fma(r6, a, b); r7 = fma(r7, a, b);
+  }
+  const double s = ((r0 + r1) + (r2 + r3)) + ((r4 + r5) + (r6 + r7));
+  if (s == 123.456) sink[0] = s;  // keeps the chains alive without a store in the common case
+}
+void launch_fp64_chain(double *sink, int iters, int blocks, cudaStream_t st) {
+  k_fp64_chain<<<blocks, 256, 0, st>>>(sink, iters);
+}
+}  // namespace jbd

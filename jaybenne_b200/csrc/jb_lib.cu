@@ -1319,4 +1319,54 @@ jb_status jb_timer_stop(jb_ctx *c, double *ms) {
 // kernels launched by this context so far (bench.py reports it as gpu_launches)
 int64_t jb_kernel_launches(const jb_ctx *c) { return c ? c->launches : 0; }
 
+jb_status jb_device_count(int32_t *n_devices) {
+  if (!n_devices) return JB_ERR_INVALID;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    n = 0;
+  }
+  *n_devices = n;
+  return n > 0 ? JB_OK : JB_ERR_NO_DEVICE;
+}
+
+jb_status jb_set_device(int32_t ordinal) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    return JB_ERR_NO_DEVICE;
+  }
+  if (ordinal < 0 || ordinal >= n) return JB_ERR_INVALID;
+  return cudaSetDevice(ordinal) == cudaSuccess ? JB_OK : JB_ERR_CUDA;
+}
+
+jb_status jb_measure_fp64_peak(jb_ctx *c, double *tflops) {
+  if (!c || !tflops) return JB_ERR_INVALID;
+  cudaSetDevice(c->device);
+  int n_sm = 0;
+  cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, c->device);
+  if (n_sm <= 0) n_sm = 148;
+  const int blocks = n_sm * 8, iters = 1 << 16;
+  cudaEvent_t e0, e1;
+  JB_CUDA(c, cudaEventCreate(&e0));
+  JB_CUDA(c, cudaEventCreate(&e1));
+  launch_fp64_chain(c->d_esum, 1 << 10, blocks, c->stream);  // warm-up
+  float best = 0.f;
+  for (int rep = 0; rep < 3; ++rep) {
+    cudaEventRecord(e0, c->stream);
+    launch_fp64_chain(c->d_esum, iters, blocks, c->stream);
+    cudaEventRecord(e1, c->stream);
+    JB_CUDA(c, cudaEventSynchronize(e1));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    if (rep == 0 || ms < best) best = ms;
+  }
+  c->launches += 4;
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  const double flops = 16.0 * (double)iters * 256.0 * (double)blocks;
+  *tflops = flops / ((double)best * 1e-3) / 1e12;
+  return JB_OK;
+}
+
 }  // extern "C"
