@@ -390,6 +390,20 @@ def main():
                 "whole_cycle_GBps": cyc_bytes / (ms * 1e-3) / 1e9,
                 "segments_per_photon": seg / max(args.steps * (last["n_start"] + last["n_sourced"]), 1)}
 
+    # second roofline (SURVEY 8d honesty note): FP64 pipe. Peak = DFMA chain kernel measured now on this GPU;
+    # flops per segment = DFMA x2 + DMUL + DADD of the kernel's main body, counted by ncu (profiles/r01_traffic.json)
+    fp64 = None
+    try:
+        fpeak = jb.measure_fp64_peak()
+        fps = float(tj.get("fp64_flops_per_segment", 317.0)) if not args.stream else 317.0
+        fach = (seg / (tr_ms * 1e-3)) * fps / 1e12 if tr_ms > 0 else 0.0
+        fp64 = {"bound": "fp64", "peak": fpeak, "unit": "TFLOP/s", "peak_source": "k_fp64_chain measured in this run",
+                "flops_per_segment": fps, "achieved": fach, "frac": fach / fpeak if fpeak > 0 else None,
+                "pipe_active_pct_ncu": ncu_pipe.get("fp64_pipe_pct")}
+    except Exception as exc:  # noqa: BLE001
+        fp64 = {"error": str(exc)}
+    roofline["fp64"] = fp64
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu_cells = min(args.cpu_cells, cells)

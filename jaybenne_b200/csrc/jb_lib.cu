@@ -268,12 +268,38 @@ static jb_status ensure_capacity(jb_ctx *c, long long need) {
   c->capacity = cap;
   if (c->n_ranks > 1) {
     c->out.cap = std::max<long long>(cap / (2 * c->n_ranks), 4096);
+    // no capacity requested: a rank that starts (nearly) empty must still be able to take what the
+    // others send it, so size the exchange buffers from the global photon count (bounded)
+    if (c->requested_capacity <= 0)
+      c->out.cap = std::max<long long>(c->out.cap, std::min<long long>(2 * c->cfg.num_particles + 4096, 1LL << 21));
     JB_CUDA(c, dalloc(&c->out.rec, c->out.cap * c->n_ranks));
     c->inbox_cap = c->out.cap * c->n_ranks;
     JB_CUDA(c, dalloc(&c->d_inbox, c->inbox_cap));
   }
   JB_CUDA(c, dalloc(&c->out.count, std::max(c->n_ranks, 1)));
   JB_CUDA(c, cudaMemset(c->out.count, 0, sizeof(unsigned long long) * std::max(c->n_ranks, 1)));
+  return JB_OK;
+}
+
+// grow only the 12 swarm arrays (Parthenon grows swarm pools on demand); the outbox / inbox keep
+// their size and content, so this is safe between packing and the NCCL send/recv
+static jb_status grow_pool_only(jb_ctx *c, long long need) {
+  if (need <= c->capacity) return JB_OK;
+  const long long cap = need + need / 4 + 1024;
+  void **arr[12];
+  swarm_arrays(c->s, arr);
+  for (int q = 0; q < 12; ++q) {
+    unsigned long long *fresh = nullptr;
+    JB_CUDA(c, dalloc(&fresh, cap));
+    if (c->n > 0) JB_CUDA(c, cudaMemcpyAsync(fresh, *arr[q], (size_t)c->n * 8, cudaMemcpyDeviceToDevice, c->stream));
+    JB_CUDA(c, cudaStreamSynchronize(c->stream));
+    dfree(*arr[q]);
+    *arr[q] = (void *)fresh;
+  }
+  dfree(c->d_tmp); dfree(c->d_perm);  // sort scratch is re-made at the new size when next needed
+  c->d_tmp = nullptr;
+  c->d_perm = nullptr;
+  c->capacity = cap;
   return JB_OK;
 }
 
@@ -727,7 +753,11 @@ static jb_status exchange_nccl(jb_ctx *c, double t_end, long long *global_sent) 
   *global_sent = total;
   if (total == 0) return JB_OK;
   if (nrecv > c->inbox_cap) return fail(c, JB_ERR_CAPACITY, "exchange inbox overflow: raise jb_set_capacity");
-  if (c->n + nrecv > c->capacity) return fail(c, JB_ERR_CAPACITY, "photon pool capacity exceeded on receive");
+  if (c->n + nrecv > c->capacity) {
+    if (c->requested_capacity > 0) return fail(c, JB_ERR_CAPACITY, "photon pool capacity exceeded on receive");
+    jb_status gs = grow_pool_only(c, c->n + nrecv);
+    if (gs != JB_OK) return gs;
+  }
   JB_NCCL(nc.GroupStart());
   long long roff = 0;
   for (int peer = 0; peer < R; ++peer) {

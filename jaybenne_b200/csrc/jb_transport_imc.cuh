@@ -95,8 +95,8 @@ __device__ __forceinline__ void imc_step_lockstep(const double xi_abs, const dou
   const double rmin = DBL_MIN;
   const double lam_abs = 1.0 / (c.ff * c.aa + rmin);
   const double lam_sc = 1.0 / (c.ss + (1.0 - c.ff) * c.aa + rmin);
-  const double dx_abs = -lam_abs * jbm::log(xi_abs);
-  const double dx_sc = -lam_sc * jbm::log(xi_sc);
+  const double dx_abs = -lam_abs * jbm::log_unit(xi_abs);
+  const double dx_sc = -lam_sc * jbm::log_unit(xi_sc);
   const double dx_end = vv * (t_end - p.t);
   double dx_push = jbm::min2(dx_cell, dx_end);
   {

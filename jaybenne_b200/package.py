@@ -242,6 +242,12 @@ class Jaybenne:
         self._check(self.api.timer_stop(self._ctx, C.byref(ms)))
         return ms.value
 
+    def measure_fp64_peak(self) -> float:
+        """Sustained FP64 FMA rate of this GPU in TFLOP/s (register-resident DFMA chains)."""
+        v = C.c_double()
+        self._check(self.api.measure_fp64_peak(self._ctx, C.byref(v)))
+        return v.value
+
     def clear_particles(self):
         self._check(self.api.set_particles(self._ctx, None, 0))
 

@@ -1905,6 +1905,7 @@ double jbo_math(int32_t fn, double x) {
     case 4: return jbm::expm1(x);
     case 5: return jbm::exp(x);
     case 6: return jbm::pow4(x);
+    case 7: return jbm::log_unit(x);
   }
   return 0.0;
 }

@@ -8,7 +8,7 @@ import numpy as np
 
 import oracle_binding as ob
 
-LOG, SIN, COS, ACOS, EXPM1, EXP, POW4 = range(7)
+LOG, SIN, COS, ACOS, EXPM1, EXP, POW4, LOG_UNIT = range(8)
 
 
 def evaluate(fn, x):
@@ -33,6 +33,18 @@ def test_log_uniform_draws():
     assert evaluate(LOG, [0.0])[0] == -np.inf
     assert np.isnan(evaluate(LOG, [-1.0])[0])
     assert evaluate(LOG, [1.0])[0] == 0.0
+
+
+def test_log_unit_equals_log_on_the_draw_lattice():
+    """log_unit (the transport kernel's logarithm) drops log's special-case branches; on uniform
+    deviates n * 2^-53 it must return log's result bit for bit, including log(0) = -inf."""
+    rng = np.random.default_rng(7)
+    n = np.concatenate([rng.integers(0, 2 ** 53, 400000, dtype=np.int64), np.arange(0, 4096, dtype=np.int64),
+                        2 ** 53 - 1 - np.arange(0, 4096, dtype=np.int64), 2 ** np.arange(0, 53, dtype=np.int64)])
+    x = n.astype(np.float64) * 1.1102230246251565e-16
+    a, b = evaluate(LOG, x), evaluate(LOG_UNIT, x)
+    assert np.array_equal(a.view(np.uint64), b.view(np.uint64))
+    assert b[np.where(n == 0)[0][0]] == -np.inf
 
 
 def test_sincos_on_zero_two_pi():
