@@ -76,6 +76,26 @@ struct Rng {
   }
 };
 
+// doubles #2*blk and #2*blk+1 of a stream in one straight-line Philox evaluation (what two
+// consecutive Rng::drand() calls starting at an even draw counter return)
+__device__ __forceinline__ void philox_pair(uint32_t blk, uint32_t id0, uint32_t id1, uint32_t id2, uint32_t k0,
+                                            uint32_t k1, double &d0, double &d1) {
+  uint32_t c0 = blk, c1 = id0, c2 = id1, c3 = id2, a = k0, b = k1;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    c0 = hi1 ^ c1 ^ a;
+    c1 = lo1;
+    c2 = hi0 ^ c3 ^ b;
+    c3 = lo0;
+    a += 0x9E3779B9u;
+    b += 0xBB67AE85u;
+  }
+  d0 = (double)((((uint64_t)c1 << 32) | c0) >> 11) * 1.1102230246251565e-16;
+  d1 = (double)((((uint64_t)c3 << 32) | c2) >> 11) * 1.1102230246251565e-16;
+}
+
 // ---------------------------------------------------------------------------------------
 // The three closures jaybenne::Initialize is handed (jaybenne.cpp:227-233), flattened to
 // plain numbers. The host fills this once (jb_lib.cu: make_closure) with the same libm
@@ -229,6 +249,27 @@ __device__ __forceinline__ void scatter_iso(Rng &rng, const double vv, double &v
   vx = vv * stheta * cs;
   vy = vv * stheta * sn;
   vz = vv * mu;
+}
+
+// Everett & Cashwell Planck sampler with the five draws handed in. d_planck_cum[l] = sum_{j<=l} j^-4
+// accumulated in the reference's order with the same IEEE operations (host-filled once, see
+// launch_source_emit), so `first l with cum[l] >= rhs` is the loop of planck.hpp:33-41 without
+// its divides.
+static __constant__ double d_planck_cum[100];
+__device__ __forceinline__ double planck_energy_draws(const Closure &cl, const double xi0, const double xi1,
+                                                      const double xi2, const double xi3, const double xi4,
+                                                      const double sb, const double temp) {
+  const double rhs = xi0 * cl.pi4 / 90.0;
+  int l = 1;
+  double ll = 1.0;
+  while (l < 100) {
+    if (d_planck_cum[l] >= rhs) {
+      ll = (double)l;
+      break;
+    }
+    l++;
+  }
+  return -(1.0 / ll) * jbm::log(xi1 * xi2 * xi3 * xi4) * sb * temp;
 }
 
 // Everett & Cashwell Planck sampler (planck.hpp:27-50); running sum of j^-4

@@ -414,19 +414,32 @@ __global__ void __launch_bounds__(256, 4) k_source_emit(StepParams P, int first_
     for (int o = lane; o < npart; o += 32) {
       const int np = pstart + o;
       const long long slot = slot0 + pglobal + o;
-      Rng rng;
-      rng.init((uint32_t)np, (uint32_t)b.gid, call, 0u, P.key0, P.key1_particle);
-      const double x = xi + b.dx[0] * (rng.drand() - 0.5);
-      const double y = yi + b.dx[1] * (rng.drand() - 0.5);
-      const double z = zi + b.dx[2] * (rng.drand() - 0.5);
-      const double theta = jbm::acos(2.0 * rng.drand() - 1.0);
-      const double phi = 2.0 * JB_PI * rng.drand();
+      // the photon's stream, draws #0..#10 in the reference's order (sourcing.cpp:175-198): x y | z mu |
+      // phi xi0 | xi1 xi2 | xi3 xi4 | t — one Philox block per pair, straight-line (same values as Rng::drand)
+      const uint32_t id0 = (uint32_t)np, id1 = (uint32_t)b.gid;
+      double d0, d1, d2, d3, d4, d5, d6, d7, d8, d9;
+      philox_pair(0u, id0, id1, call, P.key0, P.key1_particle, d0, d1);
+      philox_pair(1u, id0, id1, call, P.key0, P.key1_particle, d2, d3);
+      philox_pair(2u, id0, id1, call, P.key0, P.key1_particle, d4, d5);
+      philox_pair(3u, id0, id1, call, P.key0, P.key1_particle, d6, d7);
+      philox_pair(4u, id0, id1, call, P.key0, P.key1_particle, d8, d9);
+      const double x = xi + b.dx[0] * (d0 - 0.5);
+      const double y = yi + b.dx[1] * (d1 - 0.5);
+      const double z = zi + b.dx[2] * (d2 - 0.5);
+      const double theta = jbm::acos(2.0 * d3 - 1.0);
+      const double phi = 2.0 * JB_PI * d4;
       double st, ct, sp, cp;
       jbm::sincos(theta, &st, &ct);
       jbm::sincos(phi, &sp, &cp);
-      const double energy = planck_energy(P.cl, rng, sb, temp);
+      const double energy = planck_energy_draws(P.cl, d5, d6, d7, d8, d9, sb, temp);
       double tp = 0.;
-      if (source_type == JB_SOURCE_EMISSION) tp = t_start + rng.drand() * dt;
+      uint32_t ndraws = 10u;
+      if (source_type == JB_SOURCE_EMISSION) {
+        double d10, d11;
+        philox_pair(5u, id0, id1, call, P.key0, P.key1_particle, d10, d11);
+        tp = t_start + d10 * dt;
+        ndraws = 11u;
+      }
       P.s.x[slot] = x;
       P.s.y[slot] = y;
       P.s.z[slot] = z;
@@ -438,7 +451,7 @@ __global__ void __launch_bounds__(256, 4) k_source_emit(StepParams P, int first_
       P.s.t[slot] = tp;
       P.s.loc[slot] = make_int2(lb, ci);
       P.s.ida[slot] = make_uint2((uint32_t)np, (uint32_t)b.gid);
-      P.s.idb[slot] = make_uint2(call, rng.n);
+      P.s.idb[slot] = make_uint2(call, ndraws);
       my_n += 1;
       my_e += ew;
     }
@@ -918,6 +931,23 @@ void launch_source_emit(const StepParams &P, int first_local, int nlocal_call, i
                         double dt, uint32_t call, const long long *prefix, long long slot0, cudaStream_t st) {
   const long long ncells = (long long)nlocal_call * P.mesh.ncell;
   if (ncells <= 0) return;
+  // cumulative j^-4 table of the Planck sampler: once per device, the reference's running sum
+  static bool table_ready[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && !table_ready[dev]) {
+    double cum[100];
+    volatile double lhs = 0.0;  // volatile: one rounding per operation, no re-association
+    cum[0] = 0.0;
+    for (int l = 1; l < 100; ++l) {
+      const double j = (double)l;
+      lhs = lhs + 1.0 / ((j * j) * (j * j));
+      cum[l] = lhs;
+    }
+    cudaMemcpyToSymbolAsync(d_planck_cum, cum, sizeof(cum), 0, cudaMemcpyHostToDevice, st);
+    cudaStreamSynchronize(st);
+    table_ready[dev] = true;
+  }
   // one warp per cell, 8 warps per CTA
   k_source_emit<<<grid_for(ncells * 32, 256), 256, 0, st>>>(P, first_local, ncells, source_type, t_start, dt, call,
                                                            prefix, slot0);
