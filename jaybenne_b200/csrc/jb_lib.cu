@@ -84,6 +84,7 @@ struct jb_ctx {
   long long *d_scan = nullptr, *d_total = nullptr;
   long long *d_holes = nullptr, *d_tails = nullptr;
   long long holes_cap = 0;
+  long long n_holes = 0;              // dead slots inside [0, n) not yet squeezed out
   unsigned long long *d_counters = nullptr;  // [8] misc device counters
   double *d_esum = nullptr;
   double *d_ebins = nullptr;          // [EB_KINDS][EBINS] energy-sum bins (jb_kernels.cuh)
@@ -633,16 +634,28 @@ static jb_status census(jb_ctx *c, double t_end, long long *n_alive, long long *
   return JB_OK;
 }
 
-// squeeze out the slots whose photon is gone; needs h_stats->n_dead to be current
-static jb_status compact(jb_ctx *c, long long n_dead) {
-  if (n_dead <= 0) return JB_OK;
-  const long long n_alive = c->n - n_dead;
+// Removed photons leave holes in the pool (loc.x = -1; every kernel skips them). Like Parthenon,
+// which frees the slots of marked particles and only defragments a pool whose occupancy has
+// fallen below <jaybenne> min_swarm_occupancy (jaybenne.cpp:171-175), the pool is squeezed only
+// when fewer than max(min_swarm_occupancy, 1/2) of the used slots hold a photon, when the
+// caller needs a dense pool (swarm access, cell sort) or when room is needed (`force`).
+static jb_status compact(jb_ctx *c, long long n_dead, bool force = false) {
+  if (n_dead < 0) return fail(c, JB_ERR_STATE, "photon bookkeeping went negative");
+  c->n_holes += n_dead;
+  if (c->n_holes <= 0) return JB_OK;
+  const long long n_alive = c->n - c->n_holes;
   if (n_alive < 0) return fail(c, JB_ERR_STATE, "photon bookkeeping went negative");
+  if (!force) {
+    const double floor_occ = std::max(0.5, c->cfg.min_swarm_occupancy);
+    if ((double)n_alive >= floor_occ * (double)c->n) return JB_OK;
+  }
+  const long long holes = c->n_holes;
+  c->n_holes = 0;
   if (n_alive == 0) {
     c->n = 0;
     return JB_OK;
   }
-  const long long need = std::min(n_dead, n_alive);
+  const long long need = std::min(holes, n_alive);
   if (need > c->holes_cap) {
     dfree(c->d_holes);
     dfree(c->d_tails);
@@ -656,6 +669,7 @@ static jb_status compact(jb_ctx *c, long long n_dead) {
   c->n = n_alive;
   return JB_OK;
 }
+static jb_status ensure_dense(jb_ctx *c) { return compact(c, 0, true); }
 
 // SourcePhotons over local blocks [first, first + nb) (sourcing.cpp:25-205)
 static jb_status source_photons(jb_ctx *c, int first, int nb, int source_type, double t_start, double dt,
@@ -675,6 +689,11 @@ static jb_status source_photons(jb_ctx *c, int first, int nb, int source_type, d
   JB_CUDA(c, cudaStreamSynchronize(c->stream));
   const long long total = (long long)c->h_counters[0];
   if (total < 0 || total > 0x7fffffffLL * (long long)nb) return fail(c, JB_ERR_CAPACITY, "photon count overflow");
+  if (c->n + total > c->capacity && c->n_holes > 0) {
+    jb_status sd = ensure_dense(c);
+    if (sd != JB_OK) return sd;
+    P = make_params(c);
+  }
   if (c->n + total > c->capacity) {
     if (c->requested_capacity > 0 && c->n + total > c->requested_capacity)
       return fail(c, JB_ERR_CAPACITY, "photon pool capacity exceeded while sourcing (jb_set_capacity)");
@@ -787,6 +806,10 @@ static jb_status exchange_nccl(jb_ctx *c, double t_end, long long *global_sent) 
 // permutation is applied array by array through the one scratch array, whose storage
 // then swaps roles with the array just gathered.
 static jb_status sort_by_cell(jb_ctx *c) {
+  {
+    jb_status sd = ensure_dense(c);
+    if (sd != JB_OK) return sd;
+  }
   if (c->n <= 1) return JB_OK;
   if (c->n > 0xffffffffLL) return fail(c, JB_ERR_CAPACITY, "sort supports < 2^32 photons per rank");
   if (!c->d_tmp) {  // sort scratch is only allocated when sorting is used
@@ -1023,7 +1046,14 @@ jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats
   if (c->n_ranks > 1 && !c->comm)
     return fail(c, JB_ERR_COMM, "multi-rank step needs jb_comm_init (or drive the tasks and jb_exchange_* from the host)");
   cudaEventRecord(c->ev[0], c->stream);
-  jb_status s = stats_begin(c);
+  jb_status s = JB_OK;
+  // a fixed-size pool that also has to take arrivals from other ranks starts the cycle dense (the
+  // exchange cannot squeeze the pool between transport iterations)
+  if (c->n_ranks > 1 && c->requested_capacity > 0 && c->n_holes > 0) {
+    s = ensure_dense(c);
+    if (s != JB_OK) return s;
+  }
+  s = stats_begin(c);
   if (s != JB_OK) return s;
   s = jb_update_derived_transport_fields(c, dt);
   if (s != JB_OK) return s;
@@ -1100,6 +1130,8 @@ jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats
 // ---- swarm access ------------------------------------------------------------------------
 jb_status jb_num_particles(jb_ctx *c, int64_t *n_local) {
   JB_REQUIRE_MESH(c);
+  jb_status sd = ensure_dense(c);
+  if (sd != JB_OK) return sd;
   if (n_local) *n_local = c->n;
   return JB_OK;
 }
@@ -1107,6 +1139,10 @@ jb_status jb_num_particles(jb_ctx *c, int64_t *n_local) {
 jb_status jb_get_particles(jb_ctx *c, const jb_particles *d, int64_t capacity, int64_t *n_out) {
   JB_REQUIRE_MESH(c);
   if (!d || !n_out) return JB_ERR_INVALID;
+  {
+    jb_status sd = ensure_dense(c);
+    if (sd != JB_OK) return sd;
+  }
   const long long n = std::min<long long>(c->n, capacity);
   *n_out = n;
   if (n <= 0) return JB_OK;
@@ -1145,6 +1181,7 @@ jb_status jb_get_particles(jb_ctx *c, const jb_particles *d, int64_t capacity, i
 jb_status jb_set_particles(jb_ctx *c, const jb_particles *s, int64_t n) {
   JB_REQUIRE_MESH(c);
   if (n < 0 || (n > 0 && !s)) return JB_ERR_INVALID;
+  c->n_holes = 0;
   if (n == 0) {
     c->n = 0;
     return JB_OK;
@@ -1265,6 +1302,10 @@ jb_status jb_exchange_take(jb_ctx *c, int32_t peer, void *dst, int64_t capacity,
 jb_status jb_exchange_give_device(jb_ctx *c, const void *dev_ptr, int64_t n_records) {
   JB_REQUIRE_MESH(c);
   if (n_records <= 0) return JB_OK;
+  if (c->n + n_records > c->capacity && c->n_holes > 0) {
+    jb_status sd = ensure_dense(c);
+    if (sd != JB_OK) return sd;
+  }
   if (c->n + n_records > c->capacity) {
     if (c->requested_capacity > 0 && c->n + n_records > c->requested_capacity)
       return fail(c, JB_ERR_CAPACITY, "photon pool capacity exceeded on receive");
