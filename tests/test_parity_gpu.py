@@ -8,6 +8,7 @@ import numpy as np
 import pytest
 
 import parity_util as pu
+from jaybenne_b200 import capi
 
 pytestmark = pytest.mark.gpu
 
@@ -256,3 +257,44 @@ def test_seed_ensemble_profiles_match_reference_generator_within_3_sigma():
     o_t, o_s = _ensemble(oracle_api("std"), capi.JB_RNG_XORSHIFT_POOL, "inf", ov, 3, seeds)
     _assert_within_3_sigma(g_t.sum(axis=1, keepdims=True), o_t.sum(axis=1, keepdims=True), "inf radiation energy")
     _assert_within_3_sigma(g_s.mean(axis=1, keepdims=True), o_s.mean(axis=1, keepdims=True), "inf material sie")
+
+
+def test_gray_direct_mode_matches_oracle_and_stays_within_event_tolerance():
+    """JB_GRAY_DIRECT (sigma_a = rho * kappa instead of the reference's j_nu / B_nu round trip,
+    gray_opacity_photons.hpp:50-54): bit-exact against the oracle in the same mode, and against the
+    reference arithmetic the counts are identical and the swarm agrees to the 1e-12 event tolerance."""
+    text = pu.synthetic_text(n=16, nb=8, num_particles=20000)
+    direct = {"gray_mode": capi.JB_GRAY_DIRECT}
+    gpu, ora = pu.make_pair(text=text, cfg_overrides=direct)
+    _, ora_ref = pu.make_pair(text=text)
+    for mb in (gpu, ora, ora_ref):
+        mb.ProblemGenerator(pu.synthetic_density)
+    sg, so, sr = gpu.Step(), ora.Step(), ora_ref.Step()
+    pu.assert_stats_equal(sg, so)
+    pu.assert_swarm_equal(gpu.jb, ora.jb)
+    pu.assert_stats_equal(sg, sr)
+    pu.assert_swarm_equal(gpu.jb, ora_ref.jb, tol=1e-12, exact=False)
+
+
+def test_pool_holes_are_squeezed_by_occupancy_not_every_cycle():
+    """Absorbed photons leave holes; the pool is compacted only when occupancy drops below 1/2 (or
+    <jaybenne> min_swarm_occupancy), on swarm access, or for room. Every cycle must still match the
+    oracle, whichever state the pool is in."""
+    text = pu.synthetic_text(n=16, nb=8, num_particles=40000)
+    gpu, ora = pu.make_pair(text=text)
+    gpu.ProblemGenerator(pu.synthetic_density); ora.ProblemGenerator(pu.synthetic_density)
+    launches = []
+    for _ in range(4):                       # no swarm access in between: the pool keeps its holes
+        l0 = gpu.jb.kernel_launches()
+        sg, so = gpu.Step(), ora.Step()
+        launches.append(gpu.jb.kernel_launches() - l0)
+        pu.assert_stats_equal(sg, so)
+        assert pu.conservation_residual(sg) <= 1e-12
+    # ~1/3 of the photons are absorbed per cycle: cycle 1 stays above 1/2 occupancy (no compaction), a later one
+    # crosses it (two more launches: find + move)
+    assert max(launches) >= min(launches) + 2, launches
+    pu.assert_swarm_equal(gpu.jb, ora.jb, exact=False)
+    pu.assert_fields_equal(gpu, ora, gross=None, names=("energy_tally", "fleck_factor", "internal_energy", "sie"))
+    # a pool capped at exactly what a dense pool needs still sources: the holes are squeezed out for room
+    n_now = gpu.jb.num_particles()
+    assert n_now == sg["n_end"]
