@@ -38,7 +38,7 @@ C_LIGHT = 2.99792458e10
 SEED = 349857
 
 
-def workload_text(cells, nb, particles, stream=False):
+def workload_text(cells, nb, particles, stream=False, ddmc=False):
     from jaybenne_b200 import uniform_deck_text
     delta = 1.0 / cells
     t = uniform_deck_text([cells] * 3, [nb] * 3)
@@ -53,11 +53,13 @@ dt = {(0.5 if stream else 4.0) * delta / C_LIGHT!r}
 seed = {SEED}
 do_emission = true
 do_feedback = true
+use_ddmc = {'true' if ddmc else 'false'}
+tau_ddmc = 5.0
 <mcblock>
 opacity_model = constant
 opacity_constant_value = {0.0 if stream else 0.1 / delta!r}
 scattering_model = constant
-scattering_constant_value = {0.0 if stream else 0.5 / delta!r}
+scattering_constant_value = {0.0 if stream else (8.0 if ddmc else 0.5) / delta!r}
 initial_density = 1.0
 initial_temperature = 1.0
 initial_radiation = thermal
@@ -191,6 +193,9 @@ def main():
     ap.add_argument("--stream", action="store_true",
                     help="C5-stream variant (SURVEY 8d): dt = dx/(2c), no opacity -> ~1.4 segments per photon, the "
                          "bandwidth-bound limit of the same kernels (not the BASELINE metric's config)")
+    ap.add_argument("--ddmc", action="store_true",
+                    help="hybrid variant: use_ddmc = true, tau_ddmc = 5 with sigma*dx = 8 (every cell optically thick -> "
+                         "the DDMC kernel, transport_ddmc.cpp); not the BASELINE metric's config")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-cells", type=int, default=64)
@@ -206,6 +211,8 @@ def main():
     if args.stream:
         workload = workload.replace("C5 synthetic", "C5-stream synthetic").replace(
             "(dt = 4dx/c, kappa*dx = 0.1, sigma*dx = 0.5)", "(dt = dx/(2c), kappa = sigma = 0: free streaming)")
+    if args.ddmc:
+        workload = workload.replace("C5 synthetic", "C5-ddmc synthetic").replace("sigma*dx = 0.5)", "sigma*dx = 8, use_ddmc, tau_ddmc = 5)")
     config = {"workload": workload, "cells": cells, "meshblock": nb, "photons_per_step": particles,
               "parallelism": f"meshblocks over {world} rank(s), Z-order chunks", "l2": "inputs_exceed_l2",
               "gray_absorption": "direct" if args.gray_direct else "kirchhoff (reference arithmetic)",
@@ -241,7 +248,7 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    pin = ParameterInput(text=workload_text(cells, nb, particles, args.stream))
+    pin = ParameterInput(text=workload_text(cells, nb, particles, args.stream, args.ddmc))
     nblocks_total = (cells // nb) ** 3
     over = {"source_nblocks": nblocks_total, "sort_interval": args.sort_interval,
             "gray_mode": capi.JB_GRAY_DIRECT if args.gray_direct else capi.JB_GRAY_KIRCHHOFF}
@@ -374,13 +381,13 @@ def main():
     traffic, traffic_src, ncu_pipe = None, None, {}
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
-        if not args.stream:
+        if not args.stream and not args.ddmc:
             traffic = tj["ratio"] * tr_bytes / max(args.steps, 1)
             traffic_src = f"ncu at {tj['cells']}^3: dram bytes / algorithmic bytes = {tj['ratio']}, scaled to this launch"
             ncu_pipe = {"fp64_pipe_pct": tj.get("fp64_pipe_pct"), "issue_active_pct": tj.get("issue_active_pct")}
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "k_transport_imc", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": "k_transport<ddmc>" if args.ddmc else "k_transport_imc", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "ncu": ncu_pipe,
                 "note": "8.3 segments per photon make this kernel FP64-issue bound (~220 FP64 ops per segment against "
                         "~17 algorithmic bytes); bench.py --stream measures the same kernel in the bandwidth-bound regime",
