@@ -369,39 +369,55 @@ __device__ __forceinline__ bool fuzzy_eq(const double a, const double b, const d
   return fabs(a - b) < c * eps;  // jaybenne_utils.hpp:44-49
 }
 
+// (v1, v2, v3) of a direction sampled about `axis` (normal, then the two transverse components in
+// cyclic order) back to (vx, vy, vz): the argument orders of the reference's six call sites
+// (p.vx,p.vy,p.vz | p.vy,p.vz,p.vx | p.vz,p.vx,p.vy, transport_utils.hpp:206-262, 301-386).
+__device__ __forceinline__ void unpermute_dir(const int axis, const double v1, const double v2, const double v3,
+                                              double &vx, double &vy, double &vz) {
+  vx = axis == 0 ? v1 : (axis == 1 ? v3 : v2);
+  vy = axis == 0 ? v2 : (axis == 1 ? v1 : v3);
+  vz = axis == 0 ? v3 : (axis == 1 ? v2 : v1);
+}
+
 // DDMC interface condition for a photon that has just arrived on a cell face from an IMC
 // region (ptcl_ddmc_albedo, transport_utils.hpp:279-397): admit with the asymptotic
 // transmission probability, otherwise send it back out with a cosine-law direction.
-__device__ __forceinline__ void albedo_face(Rng &rng, const CellEnv &c, const double vv, bool &is_rejected,
-                                            const double dcell, const double vn, const double sign_in,
-                                            const double vsample, double &v1, double &v2, double &v3,
-                                            double &coord, const double coord_out) {
-  const double Pf = (2.0 / 3.0) / ((c.aa + c.ss) * dcell + 2.0 * LAM_EXT);
-  const double P = 2.0 * Pf * (1.0 + sign_in * 1.5 * vn / vv);
-  if (rng.drand() > P) {
-    face_iso_dir(vsample, rng, v1, v2, v3);
-    coord = coord_out;
-    is_rejected = true;
-  }
-}
+// The reference's six per-face branches are one evaluation here: the face is found by the same
+// tests in the same order, its parameters are selected, and the arithmetic is done once — same
+// operations on the same operands, so the same bits, without six inlined copies of the sampler
+// (profiles/r01_v4_ncu_transport_ddmc_cells64.md: 9.8 of 32 lanes active, instruction-fetch stalls).
 template <int NDIM>
 __device__ __forceinline__ void ddmc_albedo(Rng &rng, const CellEnv &c, const double vv, Photon &p,
                                             bool &is_rejected) {
   constexpr bool multi_d = NDIM >= 2, three_d = NDIM == 3;
   const double dx = c.xu - c.xl, dy = c.yu - c.yl, dz = c.zu - c.zl;
   const double tol = 2.5 * EPS_IMC;
-  if (fuzzy_eq(p.x, c.xl, dx, tol)) {
-    albedo_face(rng, c, vv, is_rejected, dx, p.vx, +1.0, -vv, p.vx, p.vy, p.vz, p.x, c.xl - EPS_IMC * dx);
-  } else if (fuzzy_eq(p.x, c.xu, dx, tol)) {
-    albedo_face(rng, c, vv, is_rejected, dx, p.vx, -1.0, vv, p.vx, p.vy, p.vz, p.x, c.xu + EPS_IMC * dx);
-  } else if (fuzzy_eq(p.y, c.yl, dy, tol) && multi_d) {
-    albedo_face(rng, c, vv, is_rejected, dy, p.vy, +1.0, -vv, p.vy, p.vz, p.vx, p.y, c.yl - EPS_IMC * dy);
-  } else if (fuzzy_eq(p.y, c.yu, dy, tol) && multi_d) {
-    albedo_face(rng, c, vv, is_rejected, dy, p.vy, -1.0, vv, p.vy, p.vz, p.vx, p.y, c.yu + EPS_IMC * dy);
-  } else if (fuzzy_eq(p.z, c.zl, dz, tol) && three_d) {
-    albedo_face(rng, c, vv, is_rejected, dz, p.vz, +1.0, -vv, p.vz, p.vx, p.vy, p.z, c.zl - EPS_IMC * dz);
-  } else if (fuzzy_eq(p.z, c.zu, dz, tol) && three_d) {
-    albedo_face(rng, c, vv, is_rejected, dz, p.vz, -1.0, vv, p.vz, p.vx, p.vy, p.z, c.zu + EPS_IMC * dz);
+  const int face = fuzzy_eq(p.x, c.xl, dx, tol) ? 0
+                 : fuzzy_eq(p.x, c.xu, dx, tol) ? 1
+                 : (fuzzy_eq(p.y, c.yl, dy, tol) && multi_d) ? 2
+                 : (fuzzy_eq(p.y, c.yu, dy, tol) && multi_d) ? 3
+                 : (fuzzy_eq(p.z, c.zl, dz, tol) && three_d) ? 4
+                 : (fuzzy_eq(p.z, c.zu, dz, tol) && three_d) ? 5 : -1;
+  if (face >= 0) {
+    const int axis = face >> 1;
+    const bool upper = (face & 1) != 0;
+    const double dcell = axis == 0 ? dx : (axis == 1 ? dy : dz);
+    const double vn = axis == 0 ? p.vx : (axis == 1 ? p.vy : p.vz);
+    const double sign_in = upper ? -1.0 : 1.0;
+    const double Pf = (2.0 / 3.0) / ((c.aa + c.ss) * dcell + 2.0 * LAM_EXT);
+    const double P = 2.0 * Pf * (1.0 + sign_in * 1.5 * vn / vv);
+    if (rng.drand() > P) {
+      double v1, v2, v3;
+      face_iso_dir(upper ? vv : -vv, rng, v1, v2, v3);
+      unpermute_dir(axis, v1, v2, v3, p.vx, p.vy, p.vz);
+      const double lo = axis == 0 ? c.xl : (axis == 1 ? c.yl : c.zl);
+      const double hi = axis == 0 ? c.xu : (axis == 1 ? c.yu : c.zu);
+      const double out = upper ? hi + EPS_IMC * dcell : lo - EPS_IMC * dcell;
+      p.x = axis == 0 ? out : p.x;
+      p.y = axis == 1 ? out : p.y;
+      p.z = axis == 2 ? out : p.z;
+      is_rejected = true;
+    }
   }
   if (!is_rejected) {
     p.x = 0.5 * (c.xl + c.xu);
@@ -413,7 +429,8 @@ __device__ __forceinline__ void ddmc_albedo(Rng &rng, const CellEnv &c, const do
 // One DDMC event (ptcl_ddmc_step, transport_utils.hpp:163-277): time to the next
 // absorption-or-leak event; pick absorb / one of six faces; a leak puts the photon just
 // inside the neighbour at the face centre with an outward cosine-law direction; no event
-// before census resamples position and direction inside the cell.
+// before census resamples position and direction inside the cell. The face is chosen by the
+// reference's cumulative thresholds (same partial sums, same order); the move is done once.
 template <int NDIM>
 __device__ __forceinline__ void ddmc_step(Rng &rng, const double t_end, const CellEnv &c, const double vv,
                                           const double P[6] /* xl, yl, zl, xu, yu, zu */, Photon &p,
@@ -425,7 +442,11 @@ __device__ __forceinline__ void ddmc_step(Rng &rng, const double t_end, const Ce
   const double leakx_l = P[0] / dx, leakx_u = P[3] / dx;
   const double leaky_l = P[1] / dy, leaky_u = P[4] / dy;
   const double leakz_l = P[2] / dz, leakz_u = P[5] / dz;
-  const double leak_tot = leakx_l + leakx_u + leaky_l + leaky_u + leakz_l + leakz_u;
+  const double th1 = leakx_l + leakx_u;
+  const double th2 = th1 + leaky_l;
+  const double th3 = th2 + leaky_u;
+  const double th4 = th3 + leakz_l;
+  const double leak_tot = th4 + leakz_u;
   const double cdf_ddmc = c.ff * c.aa + leak_tot + rmin;
   const double dt_ddmc = -jbm::log(rng.drand()) / (vv * cdf_ddmc);
   const double dt_end = t_end - p.t;
@@ -438,42 +459,23 @@ __device__ __forceinline__ void ddmc_step(Rng &rng, const double t_end, const Ce
       is_absorbed = true;
     } else if (xi < c.ff * c.aa + leak_tot) {
       const double xim = xi - c.ff * c.aa;
-      if (xim < leakx_l) {
-        p.ip -= 1;
-        p.x = c.xl - eps * dx;
-        p.y = c.yl + 0.5 * dy;
-        p.z = c.zl + 0.5 * dz;
-        face_iso_dir(-vv, rng, p.vx, p.vy, p.vz);
-      } else if (xim < leakx_l + leakx_u) {
-        p.ip += 1;
-        p.x = c.xu + eps * dx;
-        p.y = c.yl + 0.5 * dy;
-        p.z = c.zl + 0.5 * dz;
-        face_iso_dir(vv, rng, p.vx, p.vy, p.vz);
-      } else if (xim < leakx_l + leakx_u + leaky_l) {
-        p.jp -= multi_d;
-        p.y = c.yl - eps * dy;
-        p.z = c.zl + 0.5 * dz;
-        p.x = c.xl + 0.5 * dx;
-        face_iso_dir(-vv, rng, p.vy, p.vz, p.vx);
-      } else if (xim < leakx_l + leakx_u + leaky_l + leaky_u) {
-        p.jp += multi_d;
-        p.y = c.yu + eps * dy;
-        p.z = c.zl + 0.5 * dz;
-        p.x = c.xl + 0.5 * dx;
-        face_iso_dir(vv, rng, p.vy, p.vz, p.vx);
-      } else if (xim < leakx_l + leakx_u + leaky_l + leaky_u + leakz_l) {
-        p.kp -= three_d;
-        p.z = c.zl - eps * dz;
-        p.x = c.xl + 0.5 * dx;
-        p.y = c.yl + 0.5 * dy;
-        face_iso_dir(-vv, rng, p.vz, p.vx, p.vy);
-      } else if (xim <= leak_tot) {
-        p.kp += three_d;
-        p.z = c.zu + eps * dz;
-        p.x = c.xl + 0.5 * dx;
-        p.y = c.yl + 0.5 * dy;
-        face_iso_dir(vv, rng, p.vz, p.vx, p.vy);
+      const int face = xim < leakx_l ? 0 : (xim < th1 ? 1 : (xim < th2 ? 2 : (xim < th3 ? 3 : (xim < th4 ? 4 : (xim <= leak_tot ? 5 : -1)))));
+      if (face >= 0) {
+        const int axis = face >> 1;
+        const bool upper = (face & 1) != 0;
+        const int d = upper ? 1 : -1;
+        p.ip += axis == 0 ? d : 0;
+        p.jp += axis == 1 ? d * multi_d : 0;
+        p.kp += axis == 2 ? d * three_d : 0;
+        const double fx = upper ? c.xu + eps * dx : c.xl - eps * dx;
+        const double fy = upper ? c.yu + eps * dy : c.yl - eps * dy;
+        const double fz = upper ? c.zu + eps * dz : c.zl - eps * dz;
+        p.x = axis == 0 ? fx : c.xl + 0.5 * dx;
+        p.y = axis == 1 ? fy : c.yl + 0.5 * dy;
+        p.z = axis == 2 ? fz : c.zl + 0.5 * dz;
+        double v1, v2, v3;
+        face_iso_dir(upper ? vv : -vv, rng, v1, v2, v3);
+        unpermute_dir(axis, v1, v2, v3, p.vx, p.vy, p.vz);
       }
     }
   } else {

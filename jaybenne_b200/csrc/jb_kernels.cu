@@ -840,6 +840,7 @@ static void launch_transport_nd(const StepParams &P, long long first, long long 
 }
 
 #include "jb_transport_imc.cuh"
+#include "jb_transport_ddmc.cuh"
 
 void launch_transport(const StepParams &P, long long first, long long n, double t_start, double dt,
                       cudaStream_t st) {
@@ -850,6 +851,14 @@ void launch_transport(const StepParams &P, long long first, long long n, double 
       case 1: launch_transport_imc<1>(P, first, n, t_start, dt, st); break;
       case 2: launch_transport_imc<2>(P, first, n, t_start, dt, st); break;
       default: launch_transport_imc<3>(P, first, n, t_start, dt, st); break;
+    }
+    return;
+  }
+  if (dd && g_tuning.variant == 1) {  // hybrid IMC / DDMC: persistent warps with lane refill
+    switch (P.mesh.ndim) {
+      case 1: launch_transport_hybrid<1>(P, first, n, t_start, dt, st); break;
+      case 2: launch_transport_hybrid<2>(P, first, n, t_start, dt, st); break;
+      default: launch_transport_hybrid<3>(P, first, n, t_start, dt, st); break;
     }
     return;
   }

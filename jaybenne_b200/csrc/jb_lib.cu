@@ -941,7 +941,7 @@ jb_status jb_initialize_radiation(jb_ctx *c, int32_t is_thermal) {
 // photons that are gone (RemoveMarkedParticles, transport.cpp:176-178).
 static jb_status transport_range(jb_ctx *c, long long first, long long n, double t_start, double dt) {
   StepParams P = make_params(c);
-  if (c->props_dirty && !c->cfg.use_ddmc) {  // rho, sie or fleck_factor changed since the records were packed
+  if (c->props_dirty) {  // rho, sie or fleck_factor changed since the records were packed
     launch_pack_props(P, c->stream);
     c->launches += 1;
     c->props_dirty = false;

@@ -1,0 +1,282 @@
+// jb_transport_ddmc.cuh — the hybrid IMC / DDMC history kernel as persistent warps with lane refill.
+// Included by jb_kernels.cu after jb_transport_imc.cuh (shares IMC_TPB, IMC_CHUNK, load_props).
+//
+// Reference behaviour: TransportPhotons_DDMC, src/jaybenne/transport_ddmc.cpp:28-237, with
+// ptcl_transport_step / ptcl_ddmc_step / ptcl_ddmc_albedo (transport_utils.hpp:111-397), scatter
+// (scattering.hpp:21-29), SampleDDMCBlockFace for on-rank block changes (sample_ddmc_bface.cpp),
+// the swarm boundary conditions (boundaries.hpp:24-84) and the hand-over (jaybenne.cpp:26-61).
+//
+// Why: the thread-per-photon kernel (k_transport<.,true,.>) ran 9.8 of 32 lanes wide at 168
+// registers with instruction-fetch stalls (profiles/r01_v4_ncu_transport_ddmc_cells64.md): history
+// lengths differ a lot in DDMC (one census jump or many leaks), and the step functions were six
+// inlined copies each. Here a warp claims chunks of slots and refills idle lanes every iteration,
+// one iteration = one segment of the while (t < t_end) loop for every lane that holds a photon;
+// the per-face copies are folded (jb_device.cuh: ddmc_albedo / ddmc_step); the meshblock geometry
+// is re-read per segment instead of living in registers; per-cell data comes from the packed
+// CellProps record. Arithmetic and draw order are those of k_transport, so results are bit-identical.
+#ifndef JAYBENNE_B200_JB_TRANSPORT_DDMC_CUH_
+#define JAYBENNE_B200_JB_TRANSPORT_DDMC_CUH_
+
+template <int NDIM, bool LOG, int MINB>
+__global__ void __launch_bounds__(IMC_TPB, MINB)
+    k_transport_hybrid(StepParams P, long long first, long long n, double t_start, double dt, int refill_min) {
+  const DMesh &m = P.mesh;
+  constexpr bool multi_d = NDIM >= 2, three_d = NDIM == 3;
+  const double t_end = t_start + dt;
+  const double vv = P.cl.c_code;
+  const int nx1 = m.nxb[0], nx2 = m.nxb[1];
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  long long cur = 0, end = 0;
+  bool exhausted = false;
+
+  bool have = false;
+  long long idx = 0;
+  Photon p;
+  PhotonFreq q;
+  Rng rng;
+  int gid = 0;
+  p.x = p.y = p.z = p.t = p.vx = p.vy = p.vz = 0.0;
+  p.ip = p.jp = p.kp = 0;
+  q.f = q.hnu = q.bpref = 0.0;
+  rng.init(0u, 0u, 0u, 0u, P.key0, P.key1_particle);
+
+  unsigned c_seg = 0, c_ddmc = 0, c_scat = 0;
+  // energies stay per lane and are folded by a shuffle tree at the end: stiff problems absorb ~all of
+  // a large emitted energy, and the 1e-12 conservation gate is relative to the small census energy
+  double e_abs = 0.0, e_abs_c = 0.0, e_esc = 0.0;  // e_abs with a Kahan compensation term
+  __shared__ unsigned sh_cnt[8];            // crossings, absorbed, dead, escaped, sent, error, overflow
+  if (threadIdx.x < 8) sh_cnt[threadIdx.x] = 0u;
+  __syncthreads();
+
+  for (;;) {
+    // ---- refill idle lanes from the warp's chunk ---------------------------------------------
+    for (;;) {
+      if (cur >= end) {
+        if (exhausted) break;
+        unsigned long long c0 = 0;
+        if (lane == 0) c0 = atomicAdd(P.work, (unsigned long long)IMC_CHUNK);
+        c0 = __shfl_sync(FULL, c0, 0);
+        if ((long long)c0 >= n) {
+          exhausted = true;
+          break;
+        }
+        cur = first + (long long)c0;
+        end = cur + IMC_CHUNK;
+        if (end > first + n) end = first + n;
+      }
+      const unsigned need = __ballot_sync(FULL, !have);
+      const int cnt = __popc(need);
+      if (cnt < refill_min && cnt < 32) break;
+      if (cnt == 0) break;
+      const long long my = cur + __popc(need & lt_mask);
+      cur += cnt;
+      if (!have && my < end) {
+        const int2 lc = P.s.loc[my];
+        if (lc.x >= 0) {
+          const double t0 = P.s.t[my];
+          if (t0 < t_end) {  // census photons are skipped (transport_ddmc.cpp:100)
+            idx = my;
+            p.t = t0;
+            p.x = P.s.x[my]; p.y = P.s.y[my]; p.z = P.s.z[my];
+            p.vx = P.s.vx[my]; p.vy = P.s.vy[my]; p.vz = P.s.vz[my];
+            q = photon_freq(P.cl, P.s.e[my]);
+            const uint2 ia = P.s.ida[my], ib = P.s.idb[my];
+            rng.init(ia.x, ia.y, ib.x, ib.y, P.key0, P.key1_particle);
+            gid = m.local_gid[lc.x];
+            BlkReg B;
+            load_block(m, gid, B);
+            xtoijk<NDIM>(B, p, p.ip, p.jp, p.kp);  // transport_ddmc.cpp:98
+            have = true;
+          }
+        }
+      }
+    }
+    if (__ballot_sync(FULL, have) == 0u) break;
+
+    if (have) {
+      // ---- one segment, transport_ddmc.cpp:100-227 -------------------------------------------
+      const uint32_t draw0 = rng.n;
+      c_seg++;
+      BlkReg B;
+      load_block(m, gid, B);
+      const long long ci = (long long)B.lb * m.ncell + ((long long)p.kp * nx2 + p.jp) * nx1 + p.ip;
+      const CellProps cp = load_props(P.f.props + ci);
+      CellEnv c;
+      {
+        const double xcen = xc(B, m.ng[0], 0, p.ip), ycen = xc(B, m.ng[1], 1, p.jp), zcen = xc(B, m.ng[2], 2, p.kp);
+        c.xl = xcen - 0.5 * B.dx[0]; c.xu = xcen + 0.5 * B.dx[0];
+        c.yl = ycen - 0.5 * B.dx[1]; c.yu = ycen + 0.5 * B.dx[1];
+        c.zl = zcen - 0.5 * B.dx[2]; c.zu = zcen + 0.5 * B.dx[2];
+      }
+      c.ff = cp.ff;
+      c.ss = cp.ss;
+      c.aa = absorption_coeff_hoisted(P.cl, cp.rho, cp.temp, q);
+      bool is_absorbed = false, is_scattered = false, is_rejected = false;
+      const bool is_ddmc_step = B.dx_push * (c.ss + c.aa) > P.tau_ddmc;  // transport_ddmc.cpp:135
+      if (is_ddmc_step) {
+        c_ddmc++;
+        const double *fp0 = P.f.fp[0] + (size_t)B.lb * P.f.nface[0];
+        double Pf[6];
+        Pf[0] = fp0[((size_t)p.kp * nx2 + p.jp) * (nx1 + 1) + p.ip];
+        Pf[3] = fp0[((size_t)p.kp * nx2 + p.jp) * (nx1 + 1) + p.ip + 1];
+        if (multi_d) {
+          const double *fp1 = P.f.fp[1] + (size_t)B.lb * P.f.nface[1];
+          Pf[1] = fp1[((size_t)p.kp * (nx2 + 1) + p.jp) * nx1 + p.ip];
+          Pf[4] = fp1[((size_t)p.kp * (nx2 + 1) + p.jp + 1) * nx1 + p.ip];
+        } else {
+          Pf[1] = 0.0; Pf[4] = 0.0;
+        }
+        if (three_d) {
+          const double *fp2 = P.f.fp[2] + (size_t)B.lb * P.f.nface[2];
+          Pf[2] = fp2[((size_t)p.kp * nx2 + p.jp) * nx1 + p.ip];
+          Pf[5] = fp2[((size_t)(p.kp + 1) * nx2 + p.jp) * nx1 + p.ip];
+        } else {
+          Pf[2] = 0.0; Pf[5] = 0.0;
+        }
+        ddmc_albedo<NDIM>(rng, c, vv, p, is_rejected);
+        if (!is_rejected) ddmc_step<NDIM>(rng, t_end, c, vv, Pf, p, is_absorbed);
+      } else {
+        imc_step<NDIM>(rng, t_end, c, vv, B.dx_push, p, is_absorbed, is_scattered);
+      }
+      xtoijk<NDIM>(B, p, p.ip, p.jp, p.kp);
+      int kind = (is_ddmc_step ? JB_EV_DDMC : 0) | (is_rejected ? JB_EV_ALBEDO_REJECT : 0);
+      bool gone = false;
+      if (!on_block(m, p.ip, p.jp, p.kp)) {
+        // zero velocity tags a DDMC photon for block-face resampling (transport_ddmc.cpp:203-211)
+        const double vmask = !(is_ddmc_step && multi_d && !is_rejected) ? 1.0 : 0.0;
+        p.vx *= vmask;
+        p.vy *= vmask;
+        p.vz *= vmask;
+        if (LOG) {
+          const uint4 idn = make_uint4(rng.id0, rng.id1, rng.id2, 0u);
+          log_event(P, idn, draw0, kind | JB_EV_LEFT_BLOCK | (!(p.t < t_end) ? JB_EV_CENSUS : 0), B.gid, p);
+        }
+        // ---- MeshSend / MeshReceive, on device ----
+        if (!apply_swarm_bc<NDIM>(m, p)) {
+          atomicAdd(&sh_cnt[3], 1u);
+          e_esc += P.s.w[idx];
+          gone = true;
+        } else {
+          const double pos[3] = {p.x, p.y, p.z};
+          const int ngid = find_block(m, pos);
+          if (ngid < 0) {
+            atomicAdd(&sh_cnt[5], 1u);
+            gone = true;
+          } else {
+            atomicAdd(&sh_cnt[0], 1u);
+            const DBlock &nb = m.blocks[ngid];
+            if (nb.rank != m.my_rank) {
+              const unsigned long long slot = atomicAdd(&P.out.count[nb.rank], 1ull);
+              if ((long long)slot < P.out.cap) {
+                ExRecord r;
+                r.x = p.x; r.y = p.y; r.z = p.z; r.t = p.t; r.w = P.s.w[idx]; r.e = P.s.e[idx];
+                r.vx = p.vx; r.vy = p.vy; r.vz = p.vz;
+                r.rng[0] = rng.id0; r.rng[1] = rng.id1; r.rng[2] = rng.id2; r.rng[3] = rng.n;
+                r.dest_gid = ngid;
+                r.pad = 0;
+                P.out.rec[(size_t)nb.rank * P.out.cap + slot] = r;
+                atomicAdd(&sh_cnt[4], 1u);
+              } else {
+                atomicAdd(&sh_cnt[6], 1u);
+              }
+              gone = true;
+            } else {
+              gid = ngid;
+              BlkReg NB;
+              load_block(m, gid, NB);
+              xtoijk<NDIM>(NB, p, p.ip, p.jp, p.kp);
+              bface_sample<NDIM>(P, NB, p, rng);
+            }
+          }
+        }
+      } else if (is_absorbed) {
+        const double ww = P.s.w[idx];
+        atomicAdd(&P.f.edelta[(long long)B.lb * m.ncell + ((long long)p.kp * nx2 + p.jp) * nx1 + p.ip], ww);
+        atomicAdd(&sh_cnt[1], 1u);
+        {
+          const double y = ww - e_abs_c, t = e_abs + y;
+          e_abs_c = (t - e_abs) - y;
+          e_abs = t;
+        }
+        if (LOG) log_event(P, make_uint4(rng.id0, rng.id1, rng.id2, 0u), draw0, kind | JB_EV_ABSORB, B.gid, p);
+        gone = true;
+      } else {
+        if (is_scattered) {
+          scatter_iso(rng, vv, p.vx, p.vy, p.vz);
+          c_scat++;
+          kind |= JB_EV_SCATTER;
+        }
+        if (LOG)
+          log_event(P, make_uint4(rng.id0, rng.id1, rng.id2, 0u), draw0, kind | (!(p.t < t_end) ? JB_EV_CENSUS : 0),
+                    B.gid, p);
+      }
+      // ---- finished for this call? write back and free the lane -------------------------------
+      if (gone) {
+        P.s.loc[idx].x = -1;
+        atomicAdd(&sh_cnt[2], 1u);
+        have = false;
+      } else if (!(p.t < t_end)) {
+        P.s.x[idx] = p.x; P.s.y[idx] = p.y; P.s.z[idx] = p.z; P.s.t[idx] = p.t;
+        P.s.vx[idx] = p.vx; P.s.vy[idx] = p.vy; P.s.vz[idx] = p.vz;
+        P.s.loc[idx] = make_int2(m.blocks[gid].local, (p.kp * nx2 + p.jp) * nx1 + p.ip);
+        P.s.idb[idx] = make_uint2(rng.id2, rng.n);
+        have = false;
+      }
+    }
+  }
+  DStats *S = P.stats;
+  warp_add_u64(&S->n_segments, c_seg);
+  warp_add_u64(&S->n_scatters, c_scat);
+  warp_add_u64(&S->n_ddmc, c_ddmc);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (sh_cnt[0]) atomicAdd(&S->n_crossings, (unsigned long long)sh_cnt[0]);
+    if (sh_cnt[1]) atomicAdd(&S->n_absorbed, (unsigned long long)sh_cnt[1]);
+    if (sh_cnt[2]) atomicAdd(&S->n_dead, (unsigned long long)sh_cnt[2]);
+    if (sh_cnt[3]) atomicAdd(&S->n_escaped, (unsigned long long)sh_cnt[3]);
+    if (sh_cnt[4]) atomicAdd(&S->n_sent, (unsigned long long)sh_cnt[4]);
+    if (sh_cnt[5]) atomicAdd(&S->n_error, (unsigned long long)sh_cnt[5]);
+    if (sh_cnt[6]) atomicAdd(&S->n_overflow, (unsigned long long)sh_cnt[6]);
+  }
+  warp_add_energy(P, EB_ABSORBED, e_abs);
+  if (__any_sync(FULL, e_esc != 0.0)) warp_add_energy(P, EB_ESCAPED, e_esc);
+}
+
+template <int NDIM, int MINB>
+static void launch_transport_hybrid_b(const StepParams &P, long long first, long long n, double t_start, double dt,
+                                      cudaStream_t st) {
+  static int n_sm = 0;
+  if (n_sm == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    if (n_sm <= 0) n_sm = 148;
+  }
+  long long blocks = (long long)n_sm * MINB;  // persistent grid: MINB CTAs of 4 warps on each SM
+  const long long need = (n + IMC_TPB - 1) / IMC_TPB;
+  if (blocks > need) blocks = need;
+  if (blocks < 1) blocks = 1;
+  const int rf = g_tuning.refill_min;
+  if (P.log.cap > 0)
+    k_transport_hybrid<NDIM, true, 4><<<(unsigned)(blocks > n_sm * 4LL ? n_sm * 4LL : blocks), IMC_TPB, 0, st>>>(P, first, n, t_start, dt, rf);
+  else
+    k_transport_hybrid<NDIM, false, MINB><<<(unsigned)blocks, IMC_TPB, 0, st>>>(P, first, n, t_start, dt, rf);
+}
+template <int NDIM>
+static void launch_transport_hybrid(const StepParams &P, long long first, long long n, double t_start, double dt,
+                                    cudaStream_t st) {
+  static int ctas = 0;
+  if (ctas == 0) {
+    const char *v = getenv("JB_DDMC_CTAS_PER_SM");
+    ctas = v ? atoi(v) : 6;
+  }
+  switch (ctas) {
+    case 5: launch_transport_hybrid_b<NDIM, 5>(P, first, n, t_start, dt, st); break;
+    case 6: launch_transport_hybrid_b<NDIM, 6>(P, first, n, t_start, dt, st); break;
+    default: launch_transport_hybrid_b<NDIM, 4>(P, first, n, t_start, dt, st); break;
+  }
+}
+
+#endif  // JAYBENNE_B200_JB_TRANSPORT_DDMC_CUH_
