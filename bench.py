@@ -286,16 +286,14 @@ def main():
 
     def step(src_rho, src_sie, readback):
         jb.clear_particles()
-        for q, gid in enumerate(gids):
-            jb.set_field_ptr(gid, "density", src_rho[q].data_ptr())
-            jb.set_field_ptr(gid, "sie", src_sie[q].data_ptr())
+        jb.set_fields_ptr("density", gids, [src_rho[q].data_ptr() for q in range(len(gids))])
+        jb.set_fields_ptr("sie", gids, [src_sie[q].data_ptr() for q in range(len(gids))])
         jb.InitializeRadiation(True)
         jb.PostInitialization()
         st = jb.RadiationStep(0.0, dt)
         if readback:
-            for q, gid in enumerate(gids):
-                jb.get_field_ptr(gid, "energy_tally", host_tally[q].data_ptr())
-                jb.get_field_ptr(gid, "internal_energy", host_u[q].data_ptr())
+            jb.get_fields_ptr("energy_tally", gids, [host_tally[q].data_ptr() for q in range(len(gids))])
+            jb.get_fields_ptr("internal_energy", gids, [host_u[q].data_ptr() for q in range(len(gids))])
         return st
 
     def barrier():

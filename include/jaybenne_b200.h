@@ -218,6 +218,11 @@ jb_status jb_set_capacity(jb_ctx *ctx, int64_t max_particles);
  * a device pointer. gid must be a block owned by this rank. */
 jb_status jb_set_field(jb_ctx *ctx, int32_t gid, int32_t field, const double *src);
 jb_status jb_get_field(jb_ctx *ctx, int32_t gid, int32_t field, double *dst_host);
+/* The same for `n` blocks in one call (a MeshData partition: every block of the pack at once,
+ * src/jaybenne/jaybenne.cpp:285-300 iterates vmesh.GetNBlocks()): n copies queued on the library's
+ * stream, one synchronisation. gids[i] pairs with srcs[i] / dsts[i]. */
+jb_status jb_set_fields(jb_ctx *ctx, int32_t field, int32_t n, const int32_t *gids, const double *const *srcs);
+jb_status jb_get_fields(jb_ctx *ctx, int32_t field, int32_t n, const int32_t *gids, double *const *dsts_host);
 /* Multi-rank DDMC: density / sie of a block owned by ANOTHER rank (the ghost-zone exchange of
  * src/mcblock/mcblock_driver.cpp:68 + jaybenne.cpp:108-110 as one whole-block copy). Needed
  * before jb_update_derived_transport_fields only when the host program moves the data itself;

@@ -220,6 +220,15 @@ class Package {
     GetField(gid, field, v.data());
     return v;
   }
+  // every block of a pack in one call (one synchronisation): gids[i] pairs with ptrs[i]
+  void SetFields(int32_t field, const std::vector<int> &gids, const std::vector<const Real *> &srcs) {
+    std::vector<int32_t> g(gids.begin(), gids.end());
+    check(jb_set_fields(ctx_, field, (int32_t)g.size(), g.data(), srcs.data()));
+  }
+  void GetFields(int32_t field, const std::vector<int> &gids, const std::vector<Real *> &dsts) const {
+    std::vector<int32_t> g(gids.begin(), gids.end());
+    check(jb_get_fields(ctx_, field, (int32_t)g.size(), g.data(), dsts.data()));
+  }
   void SetRemoteField(int gid, int32_t field, const Real *src) { check(jb_set_remote_field(ctx_, gid, field, src)); }
 
   int64_t NumParticles() const {

@@ -161,6 +161,8 @@ DEVICE_API = {
     "exchange_give_device": (C.c_int, [ctx_p, C.c_void_p, C.c_int64]),
     "exchange_clear": (C.c_int, [ctx_p]),
     "set_remote_field": (C.c_int, [ctx_p, C.c_int32, C.c_int32, C.c_void_p]),
+    "set_fields": (C.c_int, [ctx_p, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_void_p)]),
+    "get_fields": (C.c_int, [ctx_p, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_void_p)]),
 }
 DECK_API = {
     "deck_load": (C.c_int, [C.c_char_p, C.POINTER(deck_p)]),

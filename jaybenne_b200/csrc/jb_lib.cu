@@ -574,6 +574,48 @@ jb_status jb_set_field(jb_ctx *c, int32_t gid, int32_t field, const double *src)
   c->props_dirty = true;
   return JB_OK;
 }
+jb_status jb_set_fields(jb_ctx *c, int32_t field, int32_t n, const int32_t *gids, const double *const *srcs) {
+  if (!c || n < 0 || (n > 0 && (!gids || !srcs))) return JB_ERR_INVALID;
+  if (!c->mesh_set) return fail(c, JB_ERR_STATE, "mesh not set");
+  long long nb;
+  double *p = field_ptr(c, field, &nb);
+  if (!p) return fail(c, JB_ERR_INVALID, "bad field (face probabilities exist only with use_ddmc)");
+  JB_CUDA(c, cudaSetDevice(c->device));
+  for (int32_t q = 0; q < n; ++q) {
+    const int32_t gid = gids[q];
+    if (gid < 0 || gid >= c->mesh.nblocks || c->gid_to_local[gid] < 0 || !srcs[q]) {
+      cudaStreamSynchronize(c->stream);
+      return fail(c, JB_ERR_INVALID, "block not local");
+    }
+    JB_CUDA(c, cudaMemcpyAsync(p + (size_t)c->gid_to_local[gid] * nb, srcs[q], sizeof(double) * nb, cudaMemcpyDefault,
+                               c->stream));
+  }
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->props_dirty = true;
+  return JB_OK;
+}
+jb_status jb_get_fields(jb_ctx *c, int32_t field, int32_t n, const int32_t *gids, double *const *dsts) {
+  if (!c || n < 0 || (n > 0 && (!gids || !dsts))) return JB_ERR_INVALID;
+  if (!c->mesh_set) return fail(c, JB_ERR_STATE, "mesh not set");
+  long long nb;
+  double *p = field_ptr(c, field, &nb);
+  JB_CUDA(c, cudaSetDevice(c->device));
+  for (int32_t q = 0; q < n; ++q) {
+    const int32_t gid = gids[q];
+    if (gid < 0 || gid >= c->mesh.nblocks || c->gid_to_local[gid] < 0 || !dsts[q]) {
+      cudaStreamSynchronize(c->stream);
+      return fail(c, JB_ERR_INVALID, "block not local");
+    }
+    if (!p) {
+      memset(dsts[q], 0, sizeof(double) * nb);
+      continue;
+    }
+    JB_CUDA(c, cudaMemcpyAsync(dsts[q], p + (size_t)c->gid_to_local[gid] * nb, sizeof(double) * nb, cudaMemcpyDefault,
+                               c->stream));
+  }
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return JB_OK;
+}
 // rho / sie of a block another rank owns, for hosts that move the DDMC ghost data themselves
 jb_status jb_set_remote_field(jb_ctx *c, int32_t gid, int32_t field, const double *src) {
   if (!c || !src) return JB_ERR_INVALID;

@@ -104,6 +104,19 @@ class Jaybenne:
         """`ptr`: raw host or device address of field_size(name) doubles."""
         self._check(self.api.set_field(self._ctx, gid, FIELDS[name], C.c_void_p(ptr)))
 
+    def set_fields_ptr(self, name, gids, ptrs):
+        """One call for many blocks: raw host or device addresses, one per gid (MeshData-style pack)."""
+        n = len(gids)
+        g = (C.c_int32 * n)(*gids)
+        p = (C.c_void_p * n)(*ptrs)
+        self._check(self.api.set_fields(self._ctx, FIELDS[name], n, g, p))
+
+    def get_fields_ptr(self, name, gids, ptrs):
+        n = len(gids)
+        g = (C.c_int32 * n)(*gids)
+        p = (C.c_void_p * n)(*ptrs)
+        self._check(self.api.get_fields(self._ctx, FIELDS[name], n, g, p))
+
     def set_remote_field(self, gid, name, values):
         """density / sie of a block another rank owns (multi-rank DDMC, host-driven exchange)."""
         a = np.ascontiguousarray(values, dtype=np.float64).ravel()

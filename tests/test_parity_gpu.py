@@ -298,3 +298,23 @@ def test_pool_holes_are_squeezed_by_occupancy_not_every_cycle():
     # a pool capped at exactly what a dense pool needs still sources: the holes are squeezed out for room
     n_now = gpu.jb.num_particles()
     assert n_now == sg["n_end"]
+
+
+def test_batched_field_access_equals_per_block_access():
+    """jb_set_fields / jb_get_fields (every block of a pack in one call) against jb_set_field / jb_get_field."""
+    text = pu.synthetic_text(n=16, nb=8, num_particles=4000)
+    gpu, _ = pu.make_pair(text=text)
+    gpu.ProblemGenerator(pu.synthetic_density)
+    gids = gpu.jb.local_gids
+    n = gpu.jb.field_size("density")
+    rng = np.random.default_rng(3)
+    rho = [1.0 + rng.random(n) for _ in gids]
+    gpu.jb.set_fields_ptr("density", gids, [a.ctypes.data for a in rho])
+    for g, a in zip(gids, rho):
+        assert np.array_equal(gpu.jb.get_field(g, "density").ravel(), a)
+    out = [np.empty(n) for _ in gids]
+    gpu.jb.get_fields_ptr("energy_tally", gids, [a.ctypes.data for a in out])
+    for g, a in zip(gids, out):
+        assert np.array_equal(gpu.jb.get_field(g, "energy_tally").ravel(), a)
+    with pytest.raises(Exception):
+        gpu.jb.set_fields_ptr("density", [10 ** 6], [rho[0].ctypes.data])
