@@ -962,17 +962,45 @@ void launch_source_emit(const StepParams &P, int first_local, int nlocal_call, i
                                                            prefix, slot0);
 }
 
-// EvaluateRadiationEnergy (jaybenne.cpp:547-561): tally(cell) += w / dV over census photons
+// EvaluateRadiationEnergy (jaybenne.cpp:547-561): tally(cell) += w / dV over census photons.
+// Freshly sourced photons sit cell by cell in the pool, so neighbouring lanes mostly hit the
+// same cell: runs of equal cells inside a warp are summed with a segmented shuffle scan and
+// issue one atomic per run. A warp whose lanes are spread over many cells (after transport)
+// sees few equal neighbours in its ballot and takes the plain one-atomic-per-lane path.
 __global__ void k_tally(StepParams P, long long n) {
   const DMesh &m = P.mesh;
-  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < n;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const int2 lc = P.s.loc[idx];
-    const int lb = lc.x;
-    if (lb < 0) continue;
-    const DBlock &b = m.blocks[m.local_gid[lb]];
-    const double dv = b.dx[0] * b.dx[1] * b.dx[2];
-    atomicAdd(&P.f.tally[(long long)lb * m.ncell + lc.y], P.s.w[idx] / dv);
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31u;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long n_round = ((n + 31) / 32) * 32;  // whole warps stay in the loop together
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < n_round; idx += stride) {
+    long long cell = -1;
+    double v = 0.0;
+    if (idx < n) {
+      const int2 lc = P.s.loc[idx];
+      if (lc.x >= 0) {
+        const DBlock &b = m.blocks[m.local_gid[lc.x]];
+        const double dv = b.dx[0] * b.dx[1] * b.dx[2];
+        cell = (long long)lc.x * m.ncell + lc.y;
+        v = P.s.w[idx] / dv;
+      }
+    }
+    const long long prev = __shfl_up_sync(FULL, cell, 1);
+    const bool head = lane == 0 || prev != cell;
+    const unsigned heads = __ballot_sync(FULL, head);
+    if (__popc(heads) > 16) {  // mostly distinct cells: aggregation would not pay
+      if (cell >= 0) atomicAdd(&P.f.tally[cell], v);
+      continue;
+    }
+    // segmented inclusive scan towards higher lanes; the last lane of each run holds the run's sum
+    const unsigned seg_start = 31u - __clz(heads & ((2u << lane) - 1u));  // first lane of my run
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const double up = __shfl_up_sync(FULL, v, o);
+      if (lane >= seg_start + o) v += up;
+    }
+    const bool tail = lane == 31u || ((heads >> (lane + 1)) & 1u);
+    if (tail && cell >= 0) atomicAdd(&P.f.tally[cell], v);
   }
 }
 void launch_tally(const StepParams &P, long long n, cudaStream_t st) {
