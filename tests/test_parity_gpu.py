@@ -318,3 +318,21 @@ def test_batched_field_access_equals_per_block_access():
         assert np.array_equal(gpu.jb.get_field(g, "energy_tally").ravel(), a)
     with pytest.raises(Exception):
         gpu.jb.set_fields_ptr("density", [10 ** 6], [rho[0].ctypes.data])
+
+
+def test_cell_sorted_pool_gives_identical_results():
+    """sort_interval = 1: after every cycle the pool is compacted and sorted by (meshblock, cell) (counting sort +
+    gather). Streams travel with the photons, so nothing may change except the slot order."""
+    text = pu.synthetic_text(n=16, nb=8, num_particles=30000)
+    gpu, ora = pu.make_pair(text=text, cfg_overrides={"sort_interval": 1})
+    gpu.ProblemGenerator(pu.synthetic_density); ora.ProblemGenerator(pu.synthetic_density)
+    for _ in range(3):
+        sg, so = gpu.Step(), ora.Step()
+        pu.assert_stats_equal(sg, so)
+    pu.assert_swarm_equal(gpu.jb, ora.jb, exact=False)
+    p = gpu.jb.particles()
+    ng = gpu.mesh.c.nghost
+    n1, n2, n3 = gpu.jb.nxb
+    cell = ((p["k"] - ng) * n2 + (p["j"] - ng)) * n1 + (p["i"] - ng)
+    key = p["block"].astype(np.int64) * (n1 * n2 * n3) + cell
+    assert len(key) == sg["n_end"] and np.all(np.diff(key) >= 0), "pool is not sorted by (block, cell)"
