@@ -129,6 +129,9 @@ __device__ __forceinline__ double robust_ratio(double a, double b) {
   const int sgn = (0.0 <= b) - (b < 0.0);
   return a / (b + sgn * (10 * DBL_MIN));
 }
+// the same for a denominator known to be >= +0 or NaN (B_nu of a positive frequency): sgn is 1 (or the
+// result NaN either way), so the two compares, the int -> double conversion and the multiply drop out
+__device__ __forceinline__ double robust_ratio_pos(double a, double b) { return a / (b + 10 * DBL_MIN); }
 // EPBremss::EmissivityPerNuOmega, epbremsstrahlung_opacity_photons.hpp:88-96
 __device__ __forceinline__ double epbremss_jnu(const Closure &cl, double rho, double temp, double nu) {
   const double thetaE = cl.kb * temp / (cl.me * cl.c * cl.c);

@@ -177,11 +177,14 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
   const long long gw = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
   // a warp works through chunks of IMC_CHUNK contiguous slots claimed from one device counter,
   // so no warp is left with a long static range while the rest of the GPU has drained
-  long long cur = 0, end = 0;
+  // the chunk cursor is warp-uniform and only touched by the refill: it lives in shared memory, and the
+  // slot is kept as a 32-bit offset from `first` (a rank's pool holds < 2^32 photons), which takes five
+  // registers off the per-lane state of a kernel that spills at 64
+  __shared__ unsigned sh_cur[IMC_TPB / 32], sh_end[IMC_TPB / 32];
   bool exhausted = false;
 
   bool have = false;     // this lane holds a photon in flight
-  long long idx = 0;     // its slot
+  unsigned idx32 = 0;    // its slot, relative to `first`
   Photon p;
   PhotonFreq q;
   Rng2 rng;
@@ -197,13 +200,17 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
   __shared__ unsigned sh_cnt[3];                // crossings, absorbed, dead
   __shared__ double sh_eabs[IMC_TPB / 32];      // absorbed energy, one partial sum per warp
   if (threadIdx.x < 3) sh_cnt[threadIdx.x] = 0u;
-  if (threadIdx.x < IMC_TPB / 32) sh_eabs[threadIdx.x] = 0.0;
+  if (threadIdx.x < IMC_TPB / 32) {
+    sh_eabs[threadIdx.x] = 0.0;
+    sh_cur[threadIdx.x] = sh_end[threadIdx.x] = 0u;
+  }
   __syncthreads();
   const unsigned wic = threadIdx.x >> 5;
 
   for (;;) {
     // ---- refill idle lanes from the warp's range ----------------------------------------
     for (;;) {
+      unsigned cur = sh_cur[wic], end = sh_end[wic];
       if (cur >= end) {
         if (exhausted) break;
         unsigned long long c0 = 0;
@@ -213,22 +220,29 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
           exhausted = true;
           break;
         }
-        cur = first + (long long)c0;
-        end = cur + IMC_CHUNK;
-        if (end > first + n) end = first + n;
+        cur = (unsigned)c0;
+        end = (long long)c0 + IMC_CHUNK > n ? (unsigned)n : cur + IMC_CHUNK;
       }
       const unsigned need = __ballot_sync(FULL, !have);
       const int cnt = __popc(need);
-      if (cnt < refill_min && cnt < 32) break;
-      if (cnt == 0) break;
-      const long long my = cur + __popc(need & lt_mask);
-      cur += cnt;
-      if (!have && my < end) {
+      if ((cnt < refill_min && cnt < 32) || cnt == 0) {
+        __syncwarp();
+        if (lane == 0) { sh_cur[wic] = cur; sh_end[wic] = end; }
+        __syncwarp();
+        break;
+      }
+      const unsigned my32 = cur + __popc(need & lt_mask);
+      const long long my = first + (long long)my32;
+      __syncwarp();
+      if (lane == 0) { sh_cur[wic] = cur + cnt; sh_end[wic] = end; }
+      __syncwarp();
+      const bool in_chunk = my32 < end;
+      if (!have && in_chunk) {
         const int2 lc = P.s.loc[my];
         if (lc.x >= 0) {
           const double t0 = P.s.t[my];
           if (t0 < t_end) {  // census photons of an earlier iteration are skipped (transport.cpp:98)
-            idx = my;
+            idx32 = my32;
             p.t = t0;
             p.x = P.s.x[my]; p.y = P.s.y[my]; p.z = P.s.z[my];
             p.vx = P.s.vx[my]; p.vy = P.s.vy[my]; p.vz = P.s.vz[my];
@@ -265,6 +279,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
     if (have) {
       // ---- one segment of the while (t < t_end) loop, transport.cpp:112-171 ------------
       c_seg++;
+      const long long idx = first + (long long)idx32;
       // loads first: their latency hides behind the Philox block
       const long long ci = (long long)lb * m.ncell + ((long long)p.kp * nx2 + p.jp) * nx1 + p.ip;
       const CellProps cp = load_props(P.f.props + ci);
@@ -293,7 +308,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
         const double x = q.hnu / (P.cl.kb * T);
         const double Bnu = q.bpref / jbm::expm1(x);
         const double jnu = r * P.cl.kappa * Bnu;
-        c.aa = robust_ratio(jnu, Bnu) * P.cl.length_unit;
+        c.aa = robust_ratio_pos(jnu, Bnu) * P.cl.length_unit;
       } else {
         c.aa = absorption_coeff_hoisted(P.cl, cp.rho, cp.temp, q);
       }
