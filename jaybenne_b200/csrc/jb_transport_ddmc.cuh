@@ -17,6 +17,149 @@
 #ifndef JAYBENNE_B200_JB_TRANSPORT_DDMC_CUH_
 #define JAYBENNE_B200_JB_TRANSPORT_DDMC_CUH_
 
+// ---- the step functions on the paired generator (Rng2, jb_transport_imc.cuh) -------------------
+// Every DDMC outcome consumes its draws in pairs — (dt, xi) + (mu, phi) for a leak, (dt, z) + (x, y) +
+// (mu, phi) for census — so one Philox block per pair, evaluated by all lanes of the branch together,
+// replaces the per-draw cache test of Rng (half the lanes of every call site re-evaluating a block:
+// profiles/r01_v4_ncu_transport_ddmc_cells64.md, Philox lines at 17 of 32 lanes). Same streams, same
+// draw order, same arithmetic as ddmc_albedo / ddmc_step / face_iso_dir in jb_device.cuh.
+__device__ __forceinline__ double rng2_draw1(Rng2 &r, uint32_t k0, uint32_t k1) {
+  double v;
+  if (r.n & 1u) {
+    v = Rng2::to_double(r.clo, r.chi);  // the carried half of block n >> 1
+  } else {
+    uint32_t w0, w1, w2, w3;
+    r.block(r.n >> 1, k0, k1, w0, w1, w2, w3);
+    v = Rng2::to_double(w0, w1);
+    r.clo = w2;
+    r.chi = w3;
+  }
+  r.n += 1u;
+  return v;
+}
+__device__ __forceinline__ void face_iso_dir2(const double vv, const double xi_mu, const double xi_phi, double &v1,
+                                              double &v2, double &v3) {
+  const double mu = sqrt(xi_mu);
+  const double nu = sqrt(1.0 - mu * mu);
+  const double phi = 2.0 * JB_PI * xi_phi;
+  double sn, cs;
+  jbm::sincos(phi, &sn, &cs);
+  v1 = vv * mu;
+  v2 = vv * nu * cs;
+  v3 = vv * nu * sn;
+}
+template <int NDIM>
+__device__ __forceinline__ void ddmc_albedo2(Rng2 &rng, const uint32_t k0, const uint32_t k1, const CellEnv &c,
+                                             const double vv, Photon &p, bool &is_rejected) {
+  constexpr bool multi_d = NDIM >= 2, three_d = NDIM == 3;
+  const double dx = c.xu - c.xl, dy = c.yu - c.yl, dz = c.zu - c.zl;
+  const double tol = 2.5 * EPS_IMC;
+  const int face = fuzzy_eq(p.x, c.xl, dx, tol) ? 0
+                 : fuzzy_eq(p.x, c.xu, dx, tol) ? 1
+                 : (fuzzy_eq(p.y, c.yl, dy, tol) && multi_d) ? 2
+                 : (fuzzy_eq(p.y, c.yu, dy, tol) && multi_d) ? 3
+                 : (fuzzy_eq(p.z, c.zl, dz, tol) && three_d) ? 4
+                 : (fuzzy_eq(p.z, c.zu, dz, tol) && three_d) ? 5 : -1;
+  if (face >= 0) {
+    const int axis = face >> 1;
+    const bool upper = (face & 1) != 0;
+    const double dcell = axis == 0 ? dx : (axis == 1 ? dy : dz);
+    const double vn = axis == 0 ? p.vx : (axis == 1 ? p.vy : p.vz);
+    const double sign_in = upper ? -1.0 : 1.0;
+    const double Pf = (2.0 / 3.0) / ((c.aa + c.ss) * dcell + 2.0 * LAM_EXT);
+    const double P = 2.0 * Pf * (1.0 + sign_in * 1.5 * vn / vv);
+    if (rng2_draw1(rng, k0, k1) > P) {
+      double xi_mu, xi_phi, v1, v2, v3;
+      rng.draw2(k0, k1, xi_mu, xi_phi);
+      face_iso_dir2(upper ? vv : -vv, xi_mu, xi_phi, v1, v2, v3);
+      unpermute_dir(axis, v1, v2, v3, p.vx, p.vy, p.vz);
+      const double lo = axis == 0 ? c.xl : (axis == 1 ? c.yl : c.zl);
+      const double hi = axis == 0 ? c.xu : (axis == 1 ? c.yu : c.zu);
+      const double out = upper ? hi + EPS_IMC * dcell : lo - EPS_IMC * dcell;
+      p.x = axis == 0 ? out : p.x;
+      p.y = axis == 1 ? out : p.y;
+      p.z = axis == 2 ? out : p.z;
+      is_rejected = true;
+    }
+  }
+  if (!is_rejected) {
+    p.x = 0.5 * (c.xl + c.xu);
+    p.y = 0.5 * (c.yl + c.yu);
+    p.z = 0.5 * (c.zl + c.zu);
+  }
+}
+// `resampled` reports the census branch: the position was redrawn inside the cell and the caller has to
+// re-derive the cell index the way the reference does (Xtoijk); in every other outcome ip / jp / kp are
+// already what Xtoijk returns (cell centre, or DDMC-offset beyond a face with the index moved).
+template <int NDIM>
+__device__ __forceinline__ void ddmc_step2(Rng2 &rng, const uint32_t k0, const uint32_t k1, const double t_end,
+                                           const CellEnv &c, const double vv, const double P[6], Photon &p,
+                                           bool &is_absorbed, bool &resampled) {
+  constexpr int multi_d = NDIM >= 2 ? 1 : 0, three_d = NDIM == 3 ? 1 : 0;
+  const double rmin = DBL_MIN;
+  const double eps = EPS_DDMC;
+  const double dx = c.xu - c.xl, dy = c.yu - c.yl, dz = c.zu - c.zl;
+  const double leakx_l = P[0] / dx, leakx_u = P[3] / dx;
+  const double leaky_l = P[1] / dy, leaky_u = P[4] / dy;
+  const double leakz_l = P[2] / dz, leakz_u = P[5] / dz;
+  const double th1 = leakx_l + leakx_u;
+  const double th2 = th1 + leaky_l;
+  const double th3 = th2 + leaky_u;
+  const double th4 = th3 + leakz_l;
+  const double leak_tot = th4 + leakz_u;
+  const double cdf_ddmc = c.ff * c.aa + leak_tot + rmin;
+  double xi_dt, xi_b;  // the second draw is xi of an event or z of the census resampling
+  rng.draw2(k0, k1, xi_dt, xi_b);
+  const double dt_ddmc = -jbm::log_unit(xi_dt) / (vv * cdf_ddmc);
+  const double dt_end = t_end - p.t;
+  const bool is_ddmc_event = dt_ddmc < dt_end;
+  const double dt_push = jbm::min2(dt_ddmc, dt_end);
+  p.t += dt_push;
+  if (is_ddmc_event) {
+    const double xi = cdf_ddmc * xi_b;
+    if (xi < c.ff * c.aa) {
+      is_absorbed = true;
+    } else if (xi < c.ff * c.aa + leak_tot) {
+      const double xim = xi - c.ff * c.aa;
+      const int face = xim < leakx_l ? 0 : (xim < th1 ? 1 : (xim < th2 ? 2 : (xim < th3 ? 3 : (xim < th4 ? 4 : (xim <= leak_tot ? 5 : -1)))));
+      if (face >= 0) {
+        const int axis = face >> 1;
+        const bool upper = (face & 1) != 0;
+        const int d = upper ? 1 : -1;
+        p.ip += axis == 0 ? d : 0;
+        p.jp += axis == 1 ? d * multi_d : 0;
+        p.kp += axis == 2 ? d * three_d : 0;
+        const double fx = upper ? c.xu + eps * dx : c.xl - eps * dx;
+        const double fy = upper ? c.yu + eps * dy : c.yl - eps * dy;
+        const double fz = upper ? c.zu + eps * dz : c.zl - eps * dz;
+        p.x = axis == 0 ? fx : c.xl + 0.5 * dx;
+        p.y = axis == 1 ? fy : c.yl + 0.5 * dy;
+        p.z = axis == 2 ? fz : c.zl + 0.5 * dz;
+        double xi_mu, xi_phi, v1, v2, v3;
+        rng.draw2(k0, k1, xi_mu, xi_phi);
+        face_iso_dir2(upper ? vv : -vv, xi_mu, xi_phi, v1, v2, v3);
+        unpermute_dir(axis, v1, v2, v3, p.vx, p.vy, p.vz);
+      }
+    }
+  } else {
+    resampled = true;
+    double xi_x, xi_y, xi_mu, xi_phi;
+    rng.draw2(k0, k1, xi_x, xi_y);
+    rng.draw2(k0, k1, xi_mu, xi_phi);
+    p.z = c.zl + xi_b * dz;
+    p.x = c.xl + xi_x * dx;
+    p.y = c.yl + xi_y * dy;
+    const double mu = 1.0 - 2.0 * xi_mu;
+    const double nu = sqrt(1.0 - mu * mu);
+    const double phi = 2.0 * JB_PI * xi_phi;
+    double sn, cs;
+    jbm::sincos(phi, &sn, &cs);
+    p.vz = vv * mu;
+    p.vx = vv * nu * cs;
+    p.vy = vv * nu * sn;
+  }
+}
+
 template <int NDIM, bool LOG, int MINB>
 __global__ void __launch_bounds__(IMC_TPB, MINB)
     k_transport_hybrid(StepParams P, long long first, long long n, double t_start, double dt, int refill_min) {
@@ -35,12 +178,13 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
   long long idx = 0;
   Photon p;
   PhotonFreq q;
-  Rng rng;
+  Rng2 rng;
   int gid = 0;
   p.x = p.y = p.z = p.t = p.vx = p.vy = p.vz = 0.0;
   p.ip = p.jp = p.kp = 0;
   q.f = q.hnu = q.bpref = 0.0;
-  rng.init(0u, 0u, 0u, 0u, P.key0, P.key1_particle);
+  rng.id0 = rng.id1 = rng.id2 = rng.n = rng.clo = rng.chi = 0u;
+  const uint32_t k0 = P.key0, k1 = P.key1_particle;
 
   unsigned c_seg = 0, c_ddmc = 0, c_scat = 0;
   // energies stay per lane and are folded by a shuffle tree at the end: stiff problems absorb ~all of
@@ -83,7 +227,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
             p.vx = P.s.vx[my]; p.vy = P.s.vy[my]; p.vz = P.s.vz[my];
             q = photon_freq(P.cl, P.s.e[my]);
             const uint2 ia = P.s.ida[my], ib = P.s.idb[my];
-            rng.init(ia.x, ia.y, ib.x, ib.y, P.key0, P.key1_particle);
+            rng.load(ia.x, ia.y, ib.x, ib.y, k0, k1);
             gid = m.local_gid[lc.x];
             BlkReg B;
             load_block(m, gid, B);
@@ -135,12 +279,18 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
         } else {
           Pf[2] = 0.0; Pf[5] = 0.0;
         }
-        ddmc_albedo<NDIM>(rng, c, vv, p, is_rejected);
-        if (!is_rejected) ddmc_step<NDIM>(rng, t_end, c, vv, Pf, p, is_absorbed);
+        bool resampled = false;
+        ddmc_albedo2<NDIM>(rng, k0, k1, c, vv, p, is_rejected);
+        if (!is_rejected) ddmc_step2<NDIM>(rng, k0, k1, t_end, c, vv, Pf, p, is_absorbed, resampled);
+        // Xtoijk (transport_ddmc.cpp:198) only where the position was drawn or pushed back out of the cell
+        if (is_rejected || resampled) xtoijk<NDIM>(B, p, p.ip, p.jp, p.kp);
       } else {
-        imc_step<NDIM>(rng, t_end, c, vv, B.dx_push, p, is_absorbed, is_scattered);
+        double xi_abs, xi_sc;
+        rng.draw2(k0, k1, xi_abs, xi_sc);
+        int di, dj, dk;
+        imc_step_lockstep<NDIM>(xi_abs, xi_sc, t_end, c, vv, B.dx_push, p, is_absorbed, is_scattered, di, dj, dk);
+        p.ip += di; p.jp += dj; p.kp += dk;  // the face nudges move the index exactly (see k_transport_imc)
       }
-      xtoijk<NDIM>(B, p, p.ip, p.jp, p.kp);
       int kind = (is_ddmc_step ? JB_EV_DDMC : 0) | (is_rejected ? JB_EV_ALBEDO_REJECT : 0);
       bool gone = false;
       if (!on_block(m, p.ip, p.jp, p.kp)) {
@@ -187,7 +337,10 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
               BlkReg NB;
               load_block(m, gid, NB);
               xtoijk<NDIM>(NB, p, p.ip, p.jp, p.kp);
-              bface_sample<NDIM>(P, NB, p, rng);
+              Rng g;  // the block-face sampler (rare) runs on the per-draw generator, same stream
+              g.init(rng.id0, rng.id1, rng.id2, rng.n, k0, k1);
+              bface_sample<NDIM>(P, NB, p, g);
+              if (g.n != rng.n) rng.load(rng.id0, rng.id1, rng.id2, g.n, k0, k1);
             }
           }
         }
@@ -204,7 +357,9 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
         gone = true;
       } else {
         if (is_scattered) {
-          scatter_iso(rng, vv, p.vx, p.vy, p.vz);
+          double xi_mu, xi_phi;
+          rng.draw2(k0, k1, xi_mu, xi_phi);
+          scatter_iso2(xi_mu, xi_phi, vv, p.vx, p.vy, p.vz);
           c_scat++;
           kind |= JB_EV_SCATTER;
         }
@@ -270,7 +425,7 @@ static void launch_transport_hybrid(const StepParams &P, long long first, long l
   static int ctas = 0;
   if (ctas == 0) {
     const char *v = getenv("JB_DDMC_CTAS_PER_SM");
-    ctas = v ? atoi(v) : 6;
+    ctas = v ? atoi(v) : 5;
   }
   switch (ctas) {
     case 5: launch_transport_hybrid_b<NDIM, 5>(P, first, n, t_start, dt, st); break;
