@@ -196,6 +196,10 @@ def main():
     ap.add_argument("--ddmc", action="store_true",
                     help="hybrid variant: use_ddmc = true, tau_ddmc = 5 with sigma*dx = 8 (every cell optically thick -> "
                          "the DDMC kernel, transport_ddmc.cpp); not the BASELINE metric's config")
+    ap.add_argument("--continuing", type=int, default=0, metavar="N",
+                    help="extra report: after the timed steps, one thermal initialisation followed by N consecutive "
+                         "cycles of the same simulation (emission + feedback; the population decays by ~1/3 per cycle, "
+                         "holes accumulate and are squeezed by occupancy) -> config.continuing in the JSON line")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-cells", type=int, default=64)
@@ -367,6 +371,29 @@ def main():
                "h2d_bytes_per_step": int(2 * 8 * ncell * nb_local), "d2h_bytes_per_step": int(2 * 8 * ncell * nb_local),
                "result_checksum": float(host_tally.sum().item())}
 
+    # ---- optional: a continuing simulation (steady-state behaviour of compaction / slot order)
+    continuing = None
+    if args.continuing > 0:
+        jb.clear_particles()
+        jb.set_fields_ptr("density", gids, [dev_rho[q].data_ptr() for q in range(len(gids))])
+        jb.set_fields_ptr("sie", gids, [dev_sie[q].data_ptr() for q in range(len(gids))])
+        jb.InitializeRadiation(True)
+        jb.PostInitialization()
+        barrier()
+        jb.timer_start()
+        cyc = []
+        t_now = 0.0
+        for _ in range(args.continuing):
+            st = jb.RadiationStep(t_now, dt)
+            jb.UpdateDerivedMaterial()
+            t_now += dt
+            cyc.append({"n_start": st["n_start"], "n_segments": st["n_segments"], "ms_total": st["ms_total"],
+                        "ms_transport": st["ms_transport"]})
+        cms = reduce_max(jb.timer_stop())
+        cseg = reduce_sum(sum(c["n_segments"] for c in cyc))
+        continuing = {"cycles": args.continuing, "value": cseg / (cms * 1e-3), "unit": "segments/s", "ms": cms,
+                      "per_cycle_rank0": cyc}
+
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -423,7 +450,7 @@ def main():
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "config": config, "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
                 "roofline": roofline, "cpu_baseline": cpu,
-                "transport_ms_per_step": tr_ms_max / max(args.steps, 1),
+                "transport_ms_per_step": tr_ms_max / max(args.steps, 1), "continuing": continuing,
                 "last_step": {k: last[k] for k in ("n_start", "n_sourced", "n_absorbed", "n_end", "n_sent", "n_received",
                                                     "n_segments", "n_scatters", "n_block_crossings", "n_iterations")}}
         print(json.dumps(line))
