@@ -967,8 +967,10 @@ void launch_source_emit(const StepParams &P, int first_local, int nlocal_call, i
 // same cell: runs of equal cells inside a warp are summed with a segmented shuffle scan and
 // issue one atomic per run. A warp whose lanes are spread over many cells (after transport)
 // sees few equal neighbours in its ballot and takes the plain one-atomic-per-lane path.
-__global__ void k_tally(StepParams P, long long n) {
+__global__ void k_tally(StepParams P, long long n, unsigned long long *n_alive) {
   const DMesh &m = P.mesh;
+  unsigned long long a = 0;  // census totals ride along: photons in use and the energy they carry
+  double e = 0.0;
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31u;
   const long long stride = (long long)gridDim.x * blockDim.x;
@@ -982,7 +984,10 @@ __global__ void k_tally(StepParams P, long long n) {
         const DBlock &b = m.blocks[m.local_gid[lc.x]];
         const double dv = b.dx[0] * b.dx[1] * b.dx[2];
         cell = (long long)lc.x * m.ncell + lc.y;
-        v = P.s.w[idx] / dv;
+        const double ww = P.s.w[idx];
+        v = ww / dv;
+        a++;
+        e += ww;
       }
     }
     const long long prev = __shfl_up_sync(FULL, cell, 1);
@@ -1002,11 +1007,15 @@ __global__ void k_tally(StepParams P, long long n) {
     const bool tail = lane == 31u || ((heads >> (lane + 1)) & 1u);
     if (tail && cell >= 0) atomicAdd(&P.f.tally[cell], v);
   }
+  warp_add_u64(n_alive, a);
+  warp_add_energy(P, EB_CENSUS, e);
 }
-void launch_tally(const StepParams &P, long long n, cudaStream_t st) {
+void launch_tally(const StepParams &P, long long n, unsigned long long *n_alive, double *e_sum, cudaStream_t st) {
   const long long ncells = (long long)P.mesh.nlocal * P.mesh.ncell;
   cudaMemsetAsync(P.f.tally, 0, sizeof(double) * ncells, st);
-  if (n > 0) k_tally<<<grid_for(n, 256), 256, 0, st>>>(P, n);
+  cudaMemsetAsync(P.ebins + EB_CENSUS * EBINS, 0, sizeof(double) * EBINS, st);
+  if (n > 0) k_tally<<<grid_for(n, 256), 256, 0, st>>>(P, n, n_alive);
+  launch_fold_bins(P, EB_CENSUS, e_sum, st);
 }
 
 // UpdateFluid (jaybenne.cpp:603-612): u += energy_delta / dV

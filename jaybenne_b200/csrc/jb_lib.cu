@@ -85,6 +85,11 @@ struct jb_ctx {
   long long *d_holes = nullptr, *d_tails = nullptr;
   long long holes_cap = 0;
   long long n_holes = 0;              // dead slots inside [0, n) not yet squeezed out
+  // census totals left behind by the last tally (k_tally counts photons and sums their energy on the way);
+  // valid until the swarm changes (sourcing, transport, receive, set_particles)
+  bool census_valid = false;
+  long long census_n = 0;
+  double census_e = 0.0;
   unsigned long long *d_counters = nullptr;  // [8] misc device counters
   double *d_esum = nullptr;
   double *d_ebins = nullptr;          // [EB_KINDS][EBINS] energy-sum bins (jb_kernels.cuh)
@@ -662,6 +667,11 @@ static jb_status sync_stats(jb_ctx *c) {
 
 // census: photons in use / unfinished / energy over slots [0, n)
 static jb_status census(jb_ctx *c, double t_end, long long *n_alive, long long *n_unfinished, double *e_sum) {
+  if (c->census_valid && !n_unfinished) {  // the tally that just ran already counted them
+    if (n_alive) *n_alive = c->census_n;
+    if (e_sum) *e_sum = c->census_e;
+    return JB_OK;
+  }
   StepParams P = make_params(c);
   JB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * 2, c->stream));
   JB_CUDA(c, cudaMemsetAsync(c->d_esum, 0, sizeof(double), c->stream));
@@ -743,6 +753,7 @@ static jb_status source_photons(jb_ctx *c, int first, int nb, int source_type, d
     if (s != JB_OK) return s;
     P = make_params(c);
   }
+  c->census_valid = false;
   launch_source_emit(P, first, nb, source_type, t_start, dt, call, c->d_prefix, c->n, c->stream);
   c->launches += 1;
   c->n += total;
@@ -836,6 +847,7 @@ static jb_status exchange_nccl(jb_ctx *c, double t_end, long long *global_sent) 
   JB_CUDA(c, cudaMemsetAsync(c->out.count, 0, sizeof(unsigned long long) * R, c->stream));
   if (nrecv > 0) {
     StepParams P = make_params(c);
+    c->census_valid = false;
     launch_unpack(P, c->d_inbox, nrecv, c->n, t_end, c->stream);
     if (c->cfg.use_ddmc) launch_bface_range(P, c->n, nrecv, c->stream);
     c->launches += 1 + (c->cfg.use_ddmc ? 1 : 0);
@@ -957,9 +969,17 @@ jb_status jb_source_photons(jb_ctx *c, int32_t source_type, double t_start, doub
 jb_status jb_evaluate_radiation_energy(jb_ctx *c) {
   JB_REQUIRE_MESH(c);
   StepParams P = make_params(c);
-  launch_tally(P, c->n, c->stream);
-  c->launches += c->n > 0;
+  JB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * 2, c->stream));
+  JB_CUDA(c, cudaMemsetAsync(c->d_esum, 0, sizeof(double), c->stream));
+  launch_tally(P, c->n, c->d_counters, c->d_esum, c->stream);
+  c->launches += 1 + (c->n > 0);
+  JB_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  JB_CUDA(c, cudaMemcpyAsync(c->h_counters + 2, c->d_esum, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
   JB_CUDA(c, cudaGetLastError());
+  c->census_n = (long long)c->h_counters[0];
+  memcpy(&c->census_e, c->h_counters + 2, sizeof(double));
+  c->census_valid = true;
   return JB_OK;
 }
 
@@ -988,6 +1008,7 @@ static jb_status transport_range(jb_ctx *c, long long first, long long n, double
     c->launches += 1;
     c->props_dirty = false;
   }
+  c->census_valid = false;
   JB_CUDA(c, cudaMemsetAsync(P.work, 0, sizeof(unsigned long long), c->stream));
   launch_transport(P, first, n, t_start, dt, c->stream);
   c->launches += n > 0;
@@ -1224,6 +1245,7 @@ jb_status jb_set_particles(jb_ctx *c, const jb_particles *s, int64_t n) {
   JB_REQUIRE_MESH(c);
   if (n < 0 || (n > 0 && !s)) return JB_ERR_INVALID;
   c->n_holes = 0;
+  c->census_valid = false;
   if (n == 0) {
     c->n = 0;
     return JB_OK;
@@ -1355,6 +1377,7 @@ jb_status jb_exchange_give_device(jb_ctx *c, const void *dev_ptr, int64_t n_reco
     if (s != JB_OK) return s;
   }
   StepParams P = make_params(c);
+  c->census_valid = false;
   launch_unpack(P, (const ExRecord *)dev_ptr, n_records, c->n, std::numeric_limits<double>::infinity(), c->stream);
   c->launches += 1;
   c->n += n_records;
