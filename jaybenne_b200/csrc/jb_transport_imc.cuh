@@ -184,6 +184,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
   bool exhausted = false;
 
   bool have = false;     // this lane holds a photon in flight
+  bool pend_scat = false, need_carry = false;  // see the shared extra Philox block below
   unsigned idx32 = 0;    // its slot, relative to `first`
   Photon p;
   PhotonFreq q;
@@ -248,7 +249,8 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
             p.vx = P.s.vx[my]; p.vy = P.s.vy[my]; p.vz = P.s.vz[my];
             q = photon_freq(P.cl, P.s.e[my]);
             const uint2 ia = P.s.ida[my], ib = P.s.idb[my];
-            rng.load(ia.x, ia.y, ib.x, ib.y, P.key0, P.key1_particle);
+            rng.id0 = ia.x; rng.id1 = ia.y; rng.id2 = ib.x; rng.n = ib.y;
+            need_carry = (ib.y & 1u) != 0;  // the half block an odd draw counter carries: evaluated below
             lb = lc.x;
             gid = m.local_gid[lb];
             // the stored flat cell is what Xtoijk (transport.cpp:96) returns for a photon at rest
@@ -275,6 +277,29 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
       }
     }
     if (__ballot_sync(FULL, have) == 0u) break;  // range exhausted and nothing in flight
+
+    // ---- the one extra Philox block of the iteration --------------------------------------
+    // Two rare needs for a block outside the lock-step one: a photon that scattered in its last segment
+    // (draws #n, #n+1 for the new direction) and a photon just loaded with an odd draw counter (the
+    // second half of block n >> 1, which it carries). Evaluated separately they were two divergent
+    // Philox passes per iteration at ~6 and ~2 lanes; here they share one. The scatter itself is the
+    // reference's, applied before the photon's next segment instead of right after the last one.
+    if (have && (pend_scat || need_carry)) {
+      uint32_t w0, w1, w2, w3;
+      rng.block(pend_scat ? (rng.n + 1u) >> 1 : rng.n >> 1, P.key0, P.key1_particle, w0, w1, w2, w3);
+      if (pend_scat) {
+        const bool odd = (rng.n & 1u) != 0;
+        const double xi_mu = Rng2::to_double(odd ? rng.clo : w0, odd ? rng.chi : w1);
+        const double xi_phi = Rng2::to_double(odd ? w0 : w2, odd ? w1 : w3);
+        rng.n += 2u;
+        scatter_iso2(xi_mu, xi_phi, vv, p.vx, p.vy, p.vz);
+        c_scat++;
+        pend_scat = false;
+      }
+      rng.clo = w2;
+      rng.chi = w3;
+      need_carry = false;
+    }
 
     if (have) {
       // ---- one segment of the while (t < t_end) loop, transport.cpp:112-171 ------------
@@ -395,10 +420,14 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
         atomicAdd(&sh_eabs[wic], ww);
         gone = true;
       } else if (is_scattered) {
-        double xi_mu, xi_phi;
-        rng.draw2(P.key0, P.key1_particle, xi_mu, xi_phi);
-        scatter_iso2(xi_mu, xi_phi, vv, p.vx, p.vy, p.vz);
-        c_scat++;
+        if (p.t < t_end) {
+          pend_scat = true;  // new direction from the shared extra block at the top of the next iteration
+        } else {             // scattered exactly into census (rounding): finish it here, the lane is freed below
+          double xi_mu, xi_phi;
+          rng.draw2(P.key0, P.key1_particle, xi_mu, xi_phi);
+          scatter_iso2(xi_mu, xi_phi, vv, p.vx, p.vy, p.vz);
+          c_scat++;
+        }
       }
       // ---- photon finished for this call? write it back and free the lane -----------------
       if (gone) {
