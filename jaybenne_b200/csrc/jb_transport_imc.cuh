@@ -101,25 +101,25 @@ __device__ __forceinline__ void imc_step_lockstep(const double xi_abs, const dou
   double dx_push = jbm::min2(dx_cell, dx_end);
   {
     const double face = p.vx > 0.0 ? c.xu : c.xl;
-    const double d = vv * (face - p.x) / p.vx;
+    const double d = jbm::div_normal(vv * (face - p.x), p.vx);  // |v| is 0 (result unused) or >= ~1e-7
     const double dm = jbm::min2(dx_push, d);
     dx_push = (p.vx != 0.0) ? dm : dx_push;
   }
   if (multi_d) {
     const double face = p.vy > 0.0 ? c.yu : c.yl;
-    const double d = vv * (face - p.y) / p.vy;
+    const double d = jbm::div_normal(vv * (face - p.y), p.vy);
     const double dm = jbm::min2(dx_push, d);
     dx_push = (p.vy != 0.0) ? dm : dx_push;
   }
   if (three_d) {
     const double face = p.vz > 0.0 ? c.zu : c.zl;
-    const double d = vv * (face - p.z) / p.vz;
+    const double d = jbm::div_normal(vv * (face - p.z), p.vz);
     const double dm = jbm::min2(dx_push, d);
     dx_push = (p.vz != 0.0) ? dm : dx_push;
   }
   is_absorbed = ((dx_abs < dx_push) && (dx_abs < dx_sc));
   is_scattered = (!is_absorbed && (dx_sc < dx_push));
-  const double dt_push = (is_absorbed ? dx_abs : (is_scattered ? dx_sc : dx_push)) / vv;
+  const double dt_push = jbm::div_normal(is_absorbed ? dx_abs : (is_scattered ? dx_sc : dx_push), vv);  // <= dx_cell
   p.t += dt_push;
   p.x += p.vx * dt_push;
   p.y += (multi_d ? 1.0 : 0.0) * p.vy * dt_push;
