@@ -489,9 +489,10 @@ __device__ __forceinline__ void load_block(const DMesh &m, int gid, BlkReg &B) {
 // SwarmDeviceContext::Xtoijk as interior indices; collapsed dimensions give 0
 template <int NDIM>
 __device__ __forceinline__ void xtoijk(const BlkReg &B, const Photon &p, int &i, int &j, int &k) {
-  i = (int)floor((p.x - B.xmin[0]) / B.dx[0]);
-  j = (NDIM > 1) ? (int)floor((p.y - B.xmin[1]) / B.dx[1]) : 0;
-  k = (NDIM > 2) ? (int)floor((p.z - B.xmin[2]) / B.dx[2]) : 0;
+  // cell widths are normal numbers and the offsets finite: the range-test-free quotient (jb_math.h)
+  i = (int)floor(jbm::div_normal(p.x - B.xmin[0], B.dx[0]));
+  j = (NDIM > 1) ? (int)floor(jbm::div_normal(p.y - B.xmin[1], B.dx[1])) : 0;
+  k = (NDIM > 2) ? (int)floor(jbm::div_normal(p.z - B.xmin[2], B.dx[2])) : 0;
 }
 __device__ __forceinline__ bool on_block(const DMesh &m, int i, int j, int k) {
   return i >= 0 && i < m.nxb[0] && j >= 0 && j < m.nxb[1] && k >= 0 && k < m.nxb[2];

@@ -66,8 +66,8 @@ __device__ __forceinline__ void ddmc_albedo2(Rng2 &rng, const uint32_t k0, const
     const double dcell = axis == 0 ? dx : (axis == 1 ? dy : dz);
     const double vn = axis == 0 ? p.vx : (axis == 1 ? p.vy : p.vz);
     const double sign_in = upper ? -1.0 : 1.0;
-    const double Pf = (2.0 / 3.0) / ((c.aa + c.ss) * dcell + 2.0 * LAM_EXT);
-    const double P = 2.0 * Pf * (1.0 + sign_in * 1.5 * vn / vv);
+    const double Pf = jbm::div_normal(2.0 / 3.0, (c.aa + c.ss) * dcell + 2.0 * LAM_EXT);  // denominator >= 1.42
+    const double P = 2.0 * Pf * (1.0 + jbm::div_normal(sign_in * 1.5 * vn, vv));
     if (rng2_draw1(rng, k0, k1) > P) {
       double xi_mu, xi_phi, v1, v2, v3;
       rng.draw2(k0, k1, xi_mu, xi_phi);
@@ -99,9 +99,10 @@ __device__ __forceinline__ void ddmc_step2(Rng2 &rng, const uint32_t k0, const u
   const double rmin = DBL_MIN;
   const double eps = EPS_DDMC;
   const double dx = c.xu - c.xl, dy = c.yu - c.yl, dz = c.zu - c.zl;
-  const double leakx_l = P[0] / dx, leakx_u = P[3] / dx;
-  const double leaky_l = P[1] / dy, leaky_u = P[4] / dy;
-  const double leakz_l = P[2] / dz, leakz_u = P[5] / dz;
+  // face probabilities are in [0, 1], cell widths normal: range-test-free quotients (jb_math.h)
+  const double leakx_l = jbm::div_normal(P[0], dx), leakx_u = jbm::div_normal(P[3], dx);
+  const double leaky_l = jbm::div_normal(P[1], dy), leaky_u = jbm::div_normal(P[4], dy);
+  const double leakz_l = jbm::div_normal(P[2], dz), leakz_u = jbm::div_normal(P[5], dz);
   const double th1 = leakx_l + leakx_u;
   const double th2 = th1 + leaky_l;
   const double th3 = th2 + leaky_u;

@@ -93,8 +93,9 @@ __device__ __forceinline__ void imc_step_lockstep(const double xi_abs, const dou
                                                   bool &is_absorbed, bool &is_scattered, int &di, int &dj, int &dk) {
   constexpr bool multi_d = NDIM >= 2, three_d = NDIM == 3;
   const double rmin = DBL_MIN;
-  const double lam_abs = 1.0 / (c.ff * c.aa + rmin);
-  const double lam_sc = 1.0 / (c.ss + (1.0 - c.ff) * c.aa + rmin);
+  // denominators are >= rmin = DBL_MIN (a normal number) and far below overflow: no range test needed
+  const double lam_abs = jbm::div_normal(1.0, c.ff * c.aa + rmin);
+  const double lam_sc = jbm::div_normal(1.0, c.ss + (1.0 - c.ff) * c.aa + rmin);
   const double dx_abs = -lam_abs * jbm::log_unit(xi_abs);
   const double dx_sc = -lam_sc * jbm::log_unit(xi_sc);
   const double dx_end = vv * (t_end - p.t);
