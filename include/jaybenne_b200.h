@@ -267,6 +267,10 @@ jb_status jb_timer_start(jb_ctx *ctx);
 jb_status jb_timer_stop(jb_ctx *ctx, double *ms);
 /* CUDA kernels launched by this context since jb_create (diagnostics / bench.py) */
 int64_t jb_kernel_launches(const jb_ctx *ctx);
+/* device self-test: jbm::div_normal (the range-test-free division of the kernels, csrc/jb_math.h) against the
+ * compiler's IEEE `/` on n pseudo-random operand pairs spanning the ranges the kernels use it on (exponents within
+ * +-300, numerators also 0); *mismatches = pairs whose quotients differ in any bit. tests/test_parity_gpu.py. */
+jb_status jb_selftest_division(jb_ctx *ctx, int64_t n, int64_t *mismatches);
 /* measurement helper (bench.py): sustained FP64 FMA rate of this GPU in TFLOP/s (2 flops per
  * DFMA), from a register-resident chain kernel timed with CUDA events on the context's
  * stream. It is the denominator of the FP64-pipe fraction reported beside the HBM roofline. */

@@ -153,6 +153,7 @@ DEVICE_API = {
     "device_count": (C.c_int, [C.POINTER(C.c_int32)]),
     "set_device": (C.c_int, [C.c_int32]),
     "measure_fp64_peak": (C.c_int, [ctx_p, _pd]),
+    "selftest_division": (C.c_int, [ctx_p, C.c_int64, C.POINTER(C.c_int64)]),
     "timer_start": (C.c_int, [ctx_p]),
     "timer_stop": (C.c_int, [ctx_p, _pd]),
     "comm_unique_id": (C.c_int, [C.c_void_p]),

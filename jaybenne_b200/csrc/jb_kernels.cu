@@ -1249,6 +1249,27 @@ __global__ void __launch_bounds__(256) k_fp64_chain(double *sink, int iters) {
   const double s = ((r0 + r1) + (r2 + r3)) + ((r4 + r5) + (r6 + r7));
   if (s == 123.456) sink[0] = s;  // keeps the chains alive without a store in the common case
 }
+// jb_selftest_division: div_normal(a, b) against a / b, bit for bit. Operands: sign and 52 mantissa bits
+// from Philox, exponents uniform in [-300, 300]; every 16th numerator is 0.
+__global__ void k_selftest_division(long long n, unsigned long long *mismatches) {
+  unsigned long long bad = 0;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    double u0, u1, u2, u3;
+    philox_pair(0u, (uint32_t)i, (uint32_t)(i >> 32), 0x5e1f7e57u, 0x9E3779B9u, 0xBB67AE85u, u0, u1);
+    philox_pair(1u, (uint32_t)i, (uint32_t)(i >> 32), 0x5e1f7e57u, 0x9E3779B9u, 0xBB67AE85u, u2, u3);
+    const int ea = (int)(u2 * 601.0) - 300, eb = (int)(u3 * 601.0) - 300;
+    const unsigned long long ma = (unsigned long long)(u0 * 9007199254740992.0), mb = (unsigned long long)(u1 * 9007199254740992.0);
+    double a = jbm::u2d(((unsigned long long)(1023 + ea) << 52) | (ma & 0x000fffffffffffffull) | ((ma >> 52) << 63));
+    const double b = jbm::u2d(((unsigned long long)(1023 + eb) << 52) | (mb & 0x000fffffffffffffull) | ((mb >> 52) << 63));
+    if ((i & 15) == 0) a = 0.0;
+    const double q1 = jbm::div_normal(a, b), q2 = a / b;
+    if (jbm::d2u(q1) != jbm::d2u(q2)) bad++;
+  }
+  warp_add_u64(mismatches, bad);
+}
+void launch_selftest_division(long long n, unsigned long long *mismatches, cudaStream_t st) {
+  k_selftest_division<<<148 * 8, 256, 0, st>>>(n, mismatches);
+}
 void launch_fp64_chain(double *sink, int iters, int blocks, cudaStream_t st) {
   k_fp64_chain<<<blocks, 256, 0, st>>>(sink, iters);
 }

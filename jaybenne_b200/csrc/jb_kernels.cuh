@@ -165,6 +165,7 @@ void launch_bface_range(const StepParams &P, long long first, long long n, cudaS
 // cell sort: key = blk * ncell + cell
 void launch_sort_keys(const StepParams &P, long long n, int *cell_count, cudaStream_t st);
 void launch_sort_perm(const StepParams &P, long long n, long long *cell_offset, unsigned int *perm, cudaStream_t st);
+void launch_selftest_division(long long n, unsigned long long *mismatches, cudaStream_t st);
 void launch_fp64_chain(double *sink, int iters, int blocks, cudaStream_t st);
 void launch_gather_b64(const void *src, void *dst, const unsigned int *perm, long long n, cudaStream_t st);
 

@@ -1476,6 +1476,18 @@ jb_status jb_set_device(int32_t ordinal) {
   return cudaSetDevice(ordinal) == cudaSuccess ? JB_OK : JB_ERR_CUDA;
 }
 
+jb_status jb_selftest_division(jb_ctx *c, int64_t n, int64_t *mismatches) {
+  if (!c || !mismatches || n < 0) return JB_ERR_INVALID;
+  cudaSetDevice(c->device);
+  JB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long), c->stream));
+  launch_selftest_division(n, c->d_counters, c->stream);
+  c->launches += 1;
+  JB_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  *mismatches = (int64_t)c->h_counters[0];
+  return JB_OK;
+}
+
 jb_status jb_measure_fp64_peak(jb_ctx *c, double *tflops) {
   if (!c || !tflops) return JB_ERR_INVALID;
   cudaSetDevice(c->device);

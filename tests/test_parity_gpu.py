@@ -336,3 +336,13 @@ def test_cell_sorted_pool_gives_identical_results():
     cell = ((p["k"] - ng) * n2 + (p["j"] - ng)) * n1 + (p["i"] - ng)
     key = p["block"].astype(np.int64) * (n1 * n2 * n3) + cell
     assert len(key) == sg["n_end"] and np.all(np.diff(key) >= 0), "pool is not sorted by (block, cell)"
+
+
+def test_range_test_free_division_is_the_ieee_quotient():
+    """jbm::div_normal (nvcc's fast-path sequence without the operand test and slow-path call) must return the
+    correctly rounded quotient, i.e. the bits of `/`, over the operand ranges the kernels use it on."""
+    import ctypes as C
+    gpu, _ = pu.make_pair("inf")
+    bad = C.c_int64(-1)
+    assert gpu.api.selftest_division(gpu.jb._ctx, 200_000_000, C.byref(bad)) == 0
+    assert bad.value == 0, bad.value
