@@ -346,3 +346,24 @@ def test_range_test_free_division_is_the_ieee_quotient():
     bad = C.c_int64(-1)
     assert gpu.api.selftest_division(gpu.jb._ctx, 200_000_000, C.byref(bad)) == 0
     assert bad.value == 0, bad.value
+
+
+def test_hybrid_deck_event_by_event():
+    """The IMC / DDMC hybrid kernel's event log against the oracle's on the shipped stepdiff_smr_hybrid deck (fine
+    cells IMC, coarse cells DDMC, two refinement levels): every segment of every photon — kind bits (DDMC, albedo
+    reject, left block, absorb, census), cell, block and state — in stream order."""
+    gpu, ora = pu.make_pair("stepdiff_smr_hybrid", overrides=[("jaybenne", "num_particles", 600)])
+    gpu.ProblemGenerator(); ora.ProblemGenerator()
+    cap = 2000000
+    gpu.jb.event_log_enable(cap); ora.jb.event_log_enable(cap)
+    sg, so = gpu.Step(), ora.Step()
+    pu.assert_stats_equal(sg, so)
+    eg, eo = gpu.jb.events(), ora.jb.events()
+    assert len(eg) == len(eo) and 0 < len(eg) < cap
+    assert sg["n_ddmc_segments"] > 0 and sg["n_segments"] > sg["n_ddmc_segments"]  # a true hybrid run
+    key = lambda e: np.lexsort((e["draw"], e["id_idx"], e["id_gid"], e["id_call"]))
+    eg, eo = eg[key(eg)], eo[key(eo)]
+    for f in ("id_idx", "id_gid", "id_call", "draw", "kind", "block", "i", "j", "k"):
+        assert np.array_equal(eg[f], eo[f]), f
+    for f in ("t", "x", "y", "z", "v0", "v1", "v2"):
+        assert np.array_equal(eg[f], eo[f]), f
