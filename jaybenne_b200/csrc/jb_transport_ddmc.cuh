@@ -218,16 +218,20 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
       const long long my = cur + __popc(need & lt_mask);
       cur += cnt;
       if (!have && my < end) {
-        const int2 lc = P.s.loc[my];
-        if (lc.x >= 0) {
-          const double t0 = P.s.t[my];
-          if (t0 < t_end) {  // census photons are skipped (transport_ddmc.cpp:100)
+        // all of the slot's loads ahead of the first test, as in k_transport_imc: one DRAM round trip per refill
+        const int2 lc = ld_once(&P.s.loc[my]);
+        const double t0 = ld_once(&P.s.t[my]);
+        const double l_x = ld_once(&P.s.x[my]), l_y = ld_once(&P.s.y[my]), l_z = ld_once(&P.s.z[my]);
+        const double l_vx = ld_once(&P.s.vx[my]), l_vy = ld_once(&P.s.vy[my]), l_vz = ld_once(&P.s.vz[my]);
+        const double l_e = ld_once(&P.s.e[my]);
+        const uint2 ia = ld_once(&P.s.ida[my]), ib = ld_once(&P.s.idb[my]);
+        {
+          if (lc.x >= 0 && t0 < t_end) {  // census photons are skipped (transport_ddmc.cpp:100)
             idx = my;
             p.t = t0;
-            p.x = P.s.x[my]; p.y = P.s.y[my]; p.z = P.s.z[my];
-            p.vx = P.s.vx[my]; p.vy = P.s.vy[my]; p.vz = P.s.vz[my];
-            q = photon_freq(P.cl, P.s.e[my]);
-            const uint2 ia = P.s.ida[my], ib = P.s.idb[my];
+            p.x = l_x; p.y = l_y; p.z = l_z;
+            p.vx = l_vx; p.vy = l_vy; p.vz = l_vz;
+            q = photon_freq(P.cl, l_e);
             rng.load(ia.x, ia.y, ib.x, ib.y, k0, k1);
             gid = m.local_gid[lc.x];
             BlkReg B;
