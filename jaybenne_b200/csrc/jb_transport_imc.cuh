@@ -218,12 +218,9 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
   // change, removal) count into shared memory so they do not hold registers across the loop
   unsigned c_seg = 0, c_scat = 0;
   __shared__ unsigned sh_cnt[3];                // crossings, absorbed, dead
-  __shared__ double sh_eabs[IMC_TPB / 32];      // absorbed energy, one partial sum per warp
+  double e_abs = 0.0;                           // absorbed energy of this lane's photons (a shared double add is a CAS loop)
   if (threadIdx.x < 3) sh_cnt[threadIdx.x] = 0u;
-  if (threadIdx.x < IMC_TPB / 32) {
-    sh_eabs[threadIdx.x] = 0.0;
-    sh_cur[threadIdx.x] = sh_end[threadIdx.x] = 0u;
-  }
+  if (threadIdx.x < IMC_TPB / 32) sh_cur[threadIdx.x] = sh_end[threadIdx.x] = 0u;
   __syncthreads();
   const unsigned wic = threadIdx.x >> 5;
 
@@ -443,7 +440,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
         const double ww = P.s.w[idx];
         atomicAdd(&P.f.edelta[(long long)lb * m.ncell + ((long long)p.kp * nx2 + p.jp) * nx1 + p.ip], ww);
         atomicAdd(&sh_cnt[1], 1u);
-        atomicAdd(&sh_eabs[wic], ww);
+        e_abs += ww;
         gone = true;
       } else if (is_scattered) {
         if (p.t < t_end) {
@@ -478,8 +475,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
     if (sh_cnt[1]) atomicAdd(&S->n_absorbed, (unsigned long long)sh_cnt[1]);
     if (sh_cnt[2]) atomicAdd(&S->n_dead, (unsigned long long)sh_cnt[2]);
   }
-  if (lane == 0 && sh_eabs[wic] != 0.0)
-    atomicAdd(&P.ebins[EB_ABSORBED * EBINS + (unsigned)(gw & (EBINS - 1))], sh_eabs[wic]);
+  warp_add_energy(P, EB_ABSORBED, e_abs);
 }
 
 static TransportTuning g_tuning = {1, 8, 4, 0};
