@@ -8,21 +8,32 @@ sigma*dx = 0.5, dt = 4 dx / c, emission + feedback on, seed 349857.
 One STEP = one pass of the hot path over one batch: reset the material fields, source ~1e9
 thermal photons (SourcePhotons pass 1 + 2 and the census tally), then one full radiation
 cycle (Fleck factor, emission sourcing, transport of every photon to census / absorption,
-energy tallies, fluid update). Every step therefore does the same work (~1e9 photons,
-~8.5 segments each); the swarm is cleared between steps. With N > 1 the meshblocks are
-split over the ranks in Z-order chunks (strong scaling: the problem is the same 256^3 / 1e9)
-and photons leaving a rank travel over NCCL inside jb_radiation_step.
+energy tallies, fluid update). The per-photon streams are restarted every step
+(jb_reset_streams), so every step is the SAME batch (~1e9 photons, ~8.3 segments each) and
+`invariants` (counts and energy sums all-reduced over the ranks) must be equal for every N,
+K and W. With N > 1 the meshblocks are split over the ranks in Z-order chunks (strong
+scaling: the problem is the same 256^3 / 1e9) and photons leaving a rank travel over NVLink
+inside jb_radiation_step.
 
   value   segments of all ranks / device time (CUDA events on the library's stream, max
           over ranks), inputs resident in HBM.
   e2e     same steps through the C ABI with HOST buffers: rho, sie copied from pinned host
           memory every step, energy_tally and internal_energy read back every step.
-  roofline  transport kernel (k_transport): algorithmic bytes per launch
-          84 B x (photons in + photons out) + 32 B x cells, over its own CUDA-event time.
-  cpu_baseline  the CPU oracle (reference per-particle headers, OpenMP over photons, the
-          reference's XorShift64 pool with one state per thread) on a 64^3-cell twin of the same workload on the box's host cores (rank 0, N = 1 only).
+  roofline  the transport kernel: algorithmic bytes per launch = 84 B x (photons in +
+          photons out) + 32 B x cells, over its own CUDA-event time; `whole_cycle_GBps` uses
+          SURVEY 8d's per-cycle bytes (... + 84 B x sourced + 40 B x cells) over the step.
+          roofline.fp64 = the FP64 pipe (the bound that actually applies at 8.3 segments
+          per photon), against a DFMA-chain peak measured in the same run.
+  variants  timed in the same run, each a few seconds: `continuing` (8 consecutive cycles of one
+          simulation), `continuing_sorted` (same, pool re-sorted by cell every cycle), `ddmc`
+          (128^3 optically thick, k_transport_hybrid) and `stream` (free streaming).
+  cpu_baseline  the CPU oracle (reference per-particle headers, OpenMP over the photons of
+          all blocks, the reference's XorShift64 pool with one state per thread) on a
+          64^3-cell twin of the same workload on the box's host cores (rank 0, N = 1 only).
 
-`--impl reference` times that CPU implementation alone (rank 0; other ranks exit 0).
+`--impl reference` times that CPU implementation alone (rank 0; other ranks exit 0); its
+`config` names the twin it ran and its `cores` is what OpenMP reports after this script set
+the thread count itself.
 """
 import argparse
 import json
@@ -128,9 +139,12 @@ class ClockSampler(threading.Thread):
 def cpu_arm(cells, nb, particles, steps, warmup, budget_s=300.0):
     """The reference's CPU implementation of the path (oracle) on the host cores.
 
-    Returns (segments/s, ms/step, info). Each step is the same sequence as a GPU step on
-    a bounded twin of the workload (same per-cell loading); if the first step shows that
-    steps+warmup would not fit the time budget, the twin is shrunk once.
+    Returns (segments/s, ms/step, info). Each step is the same sequence as a GPU step on a bounded twin of the
+    workload (same per-cell loading). The thread count is set here (all cores this process may run on) and the
+    count OpenMP then reports is what `cores` says — `torch.distributed.run` exports OMP_NUM_THREADS=1 for
+    N > 1, which must not shrink the baseline. If the first step shows that steps + warmup would not fit the
+    time budget, the twin is halved per dimension ONCE and `info` (-> the line's `config`) says so.
+    Parses the deck through the host-only libjb_host.so: the CUDA library is not mapped by this arm.
     """
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_binding as ob
@@ -142,7 +156,12 @@ def cpu_arm(cells, nb, particles, steps, warmup, budget_s=300.0):
     else:
         flavour, kind = "fast", "port"
     api = ob.oracle_api(flavour)
-    cores = os.cpu_count() or 1
+    try:
+        want = len(os.sched_getaffinity(0))
+    except AttributeError:
+        want = os.cpu_count() or 1
+    api.set_num_threads(want)
+    cores = int(api.max_threads())
 
     def make(cells_, particles_):
         pin = ParameterInput(text=workload_text(cells_, min(nb, cells_), particles_))
@@ -155,15 +174,18 @@ def cpu_arm(cells, nb, particles, steps, warmup, budget_s=300.0):
         mb.ProblemGenerator(density)           # fields + thermal sourcing + tally
         return mb.jb.RadiationStep(0.0, mb.cfg.dt)
 
+    requested = (cells, particles)
     mb = make(cells, particles)
     t0 = time.perf_counter()
     st = one_step(mb)
     t_first = time.perf_counter() - t0
     done_warm = 1
+    shrunk = False
     if t_first * (steps + warmup) > budget_s and cells > 32:
         cells, particles = cells // 2, particles // 8
         mb = make(cells, particles)
         done_warm = 0
+        shrunk = True
     for _ in range(max(warmup - done_warm, 0)):
         one_step(mb)
     seg = 0
@@ -172,9 +194,14 @@ def cpu_arm(cells, nb, particles, steps, warmup, budget_s=300.0):
         st = one_step(mb)
         seg += st["n_segments"]
     el = time.perf_counter() - t0
-    info = {"kind": kind, "cores": cores, "flavour": api.flavour().decode(),
+    info = {"kind": kind, "cores": cores, "flavour": api.flavour().decode(), "cells": cells, "meshblock": min(nb, cells),
+            "photons_per_step": particles, "shrunk_to_fit_time_budget": shrunk,
+            "requested_twin": {"cells": requested[0], "photons_per_step": requested[1]},
+            "omp_num_threads_env": os.environ.get("OMP_NUM_THREADS"),
+            "cuda_library_mapped": any("libjaybenne_b200" in l for l in open("/proc/self/maps")),
             "sample": f"{cells}^3-cell twin of the workload (same per-cell loading), {particles} photons, "
-                      f"{steps} step(s): thermal sourcing + one cycle, OpenMP over photons, one XorShift64 pool state per thread as in the reference"}
+                      f"{steps} step(s): thermal sourcing + one cycle, OpenMP over the photons of all blocks on {cores} "
+                      f"threads, one XorShift64 pool state per thread as in the reference"}
     return seg / el, 1e3 * el / max(steps, 1), info
 
 
@@ -200,6 +227,8 @@ def main():
                     help="extra report: after the timed steps, one thermal initialisation followed by N consecutive "
                          "cycles of the same simulation (emission + feedback; the population decays by ~1/3 per cycle, "
                          "holes accumulate and are squeezed by occupancy) -> config.continuing in the JSON line")
+    ap.add_argument("--no-variants", dest="variants", action="store_false",
+                    help="skip the `variants` legs (continuing run, sorted continuing run, DDMC at 128^3, free streaming)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-cells", type=int, default=64)
@@ -229,10 +258,20 @@ def main():
         cpu_cells = min(args.cpu_cells, cells)
         cpu_particles = int(round(particles * (cpu_cells / cells) ** 3))
         v, ms, info = cpu_arm(cpu_cells, nb, cpu_particles, args.steps, args.warmup)
+        # `config` names what THIS arm ran: a bounded twin of the GPU arm's workload (same per-cell loading,
+        # same physics, fewer cells) — the rates are comparable, the problem sizes are not the same
+        ref_config = {"workload": workload.replace(f"{cells}^3 cells", f"{info['cells']}^3 cells (CPU twin of the {cells}^3 workload)")
+                                          .replace(f"{particles} thermal", f"{info['photons_per_step']} thermal"),
+                      "cells": info["cells"], "meshblock": info["meshblock"], "photons_per_step": info["photons_per_step"],
+                      "twin_of": {"cells": cells, "photons_per_step": particles},
+                      "shrunk_to_fit_time_budget": info["shrunk_to_fit_time_budget"], "requested_twin": info["requested_twin"],
+                      "parallelism": f"OpenMP, {info['cores']} threads (omp_get_max_threads), one process",
+                      "omp_num_threads_env": info["omp_num_threads_env"], "cuda_library_mapped": info["cuda_library_mapped"],
+                      "gray_absorption": "kirchhoff (reference arithmetic)", "rng": "XorShift64 pool, one state per thread"}
         line = {"impl": "reference", "metric": "IMC particle-segments/sec", "value": v, "unit": "segments/s",
                 "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-                "data": "synthetic", "config": config,
+                "data": "synthetic", "config": ref_config,
                 "cpu_baseline": {"value": v, "unit": "segments/s", "cores": info["cores"], "kind": info["kind"],
                                  "sample": info["sample"]},
                 "e2e": {"value": v, "unit": "segments/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -241,6 +280,7 @@ def main():
         return 0
 
     # ------------------------------------------------------------------------- our arm
+    import ctypes as C
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -252,147 +292,197 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    pin = ParameterInput(text=workload_text(cells, nb, particles, args.stream, args.ddmc))
-    nblocks_total = (cells // nb) ** 3
-    over = {"source_nblocks": nblocks_total, "sort_interval": args.sort_interval,
-            "gray_mode": capi.JB_GRAY_DIRECT if args.gray_direct else capi.JB_GRAY_KIRCHHOFF}
-    # thermal photons + one cycle's emission (particles / nblocks_total, sourcing.cpp:68-69) + slack for the
-    # uneven spread of photons over ranks
-    cap = int(particles * (1.0 + 1.0 / nblocks_total) / world * (1.02 if world == 1 else 1.25)) + 200000
-    mb = Mcblock(pin, rank=rank, n_ranks=world, capacity=cap, cfg_overrides=over)
-    jb = mb.jb
-    if world > 1:
-        idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            import ctypes as C
-            raw = C.create_string_buffer(128)
-            assert jb.api.comm_unique_id(raw) == 0, "ncclGetUniqueId failed"
-            idbuf.copy_(torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8))
-        dist.broadcast(idbuf, 0)
-        jb.comm_init(bytes(idbuf.cpu().numpy().tobytes()))
-
-    # material inputs: device-resident copies (value arm) and pinned host copies (e2e arm)
-    n1 = nb
-    ncell = n1 ** 3
-    gids = jb.local_gids
-    host_rho = torch.empty((len(gids), ncell), dtype=torch.float64, pin_memory=True)
-    host_sie = torch.empty((len(gids), ncell), dtype=torch.float64, pin_memory=True)
-    host_tally = torch.empty((len(gids), ncell), dtype=torch.float64, pin_memory=True)
-    host_u = torch.empty((len(gids), ncell), dtype=torch.float64, pin_memory=True)
-    cv = mb.cfg.eos_cv
-    for q, gid in enumerate(gids):
-        xc = mb.mesh.cell_centers(gid)
-        rho = density(xc[0][None, None, :], xc[1][None, :, None], xc[2][:, None, None])
-        host_rho[q] = torch.from_numpy(np.ascontiguousarray(rho).ravel())
-        host_sie[q] = cv * mb.tt0
-    dev_rho, dev_sie = host_rho.cuda(), host_sie.cuda()
-    dt = mb.cfg.dt
-
-    def step(src_rho, src_sie, readback):
-        jb.clear_particles()
-        jb.set_fields_ptr("density", gids, [src_rho[q].data_ptr() for q in range(len(gids))])
-        jb.set_fields_ptr("sie", gids, [src_sie[q].data_ptr() for q in range(len(gids))])
-        jb.InitializeRadiation(True)
-        jb.PostInitialization()
-        st = jb.RadiationStep(0.0, dt)
-        if readback:
-            jb.get_fields_ptr("energy_tally", gids, [host_tally[q].data_ptr() for q in range(len(gids))])
-            jb.get_fields_ptr("internal_energy", gids, [host_u[q].data_ptr() for q in range(len(gids))])
-        return st
-
     def barrier():
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def reduce_sum(x):
+    def reduce(vals, op="sum"):
+        """all-reduce a list of numbers (float64: exact for counts below 2^53)"""
         if world == 1:
-            return x
-        t = torch.tensor([float(x)], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t)
-        return float(t.item())
+            return [float(v) for v in vals]
+        t = torch.tensor([float(v) for v in vals], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
+        return [float(v) for v in t.cpu()]
 
-    def reduce_max(x):
-        if world == 1:
-            return x
-        t = torch.tensor([float(x)], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+    class Workload:
+        """One configuration resident on this rank's GPU: context, material inputs on the device and in
+        pinned host memory, and the step (= one pass of the hot path over one batch)."""
 
+        def __init__(self, cells_, nb_, particles_, stream=False, ddmc=False, sort_interval=0, gray_direct=False):
+            self.cells, self.nb, self.particles = cells_, nb_, particles_
+            pin = ParameterInput(text=workload_text(cells_, nb_, particles_, stream, ddmc))
+            nblocks_total = (cells_ // nb_) ** 3
+            over = {"source_nblocks": nblocks_total, "sort_interval": sort_interval,
+                    "gray_mode": capi.JB_GRAY_DIRECT if gray_direct else capi.JB_GRAY_KIRCHHOFF}
+            # thermal photons + one cycle's emission (particles / nblocks_total, sourcing.cpp:68-69) + slack for
+            # the uneven spread of photons over ranks
+            cap = int(particles_ * (1.0 + 1.0 / nblocks_total) / world * (1.02 if world == 1 else 1.25)) + 200000
+            self.mb = Mcblock(pin, rank=rank, n_ranks=world, capacity=cap, cfg_overrides=over)
+            self.jb = jb = self.mb.jb
+            if world > 1:
+                idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+                if rank == 0:
+                    raw = C.create_string_buffer(128)
+                    assert jb.api.comm_unique_id(raw) == 0, "ncclGetUniqueId failed"
+                    idbuf.copy_(torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8))
+                dist.broadcast(idbuf, 0)
+                jb.comm_init(bytes(idbuf.cpu().numpy().tobytes()))
+            self.ncell = nb_ ** 3
+            self.gids = gids = jb.local_gids
+            shape = (len(gids), self.ncell)
+            self.host_rho = torch.empty(shape, dtype=torch.float64, pin_memory=True)
+            self.host_sie = torch.empty(shape, dtype=torch.float64, pin_memory=True)
+            self.host_tally = torch.empty(shape, dtype=torch.float64, pin_memory=True)
+            self.host_u = torch.empty(shape, dtype=torch.float64, pin_memory=True)
+            cv = self.mb.cfg.eos_cv
+            for q, gid in enumerate(gids):
+                xc = self.mb.mesh.cell_centers(gid)
+                rho = density(xc[0][None, None, :], xc[1][None, :, None], xc[2][:, None, None])
+                self.host_rho[q] = torch.from_numpy(np.ascontiguousarray(rho).ravel())
+                self.host_sie[q] = cv * self.mb.tt0
+            self.dev_rho, self.dev_sie = self.host_rho.cuda(), self.host_sie.cuda()
+            self.dt = self.mb.cfg.dt
+
+        def ptrs(self, t):
+            return [t[q].data_ptr() for q in range(len(self.gids))]
+
+        def load(self, host):
+            jb = self.jb
+            jb.clear_particles()
+            jb.reset_streams()      # every step sees the same photons: the steps are identical batches
+            jb.set_fields_ptr("density", self.gids, self.ptrs(self.host_rho if host else self.dev_rho))
+            jb.set_fields_ptr("sie", self.gids, self.ptrs(self.host_sie if host else self.dev_sie))
+            jb.InitializeRadiation(True)
+            jb.PostInitialization()
+
+        def step(self, host=False):
+            self.load(host)
+            st = self.jb.RadiationStep(0.0, self.dt)
+            if host:
+                self.read_back()
+            return st
+
+        def read_back(self):
+            self.jb.get_fields_ptr("energy_tally", self.gids, self.ptrs(self.host_tally))
+            self.jb.get_fields_ptr("internal_energy", self.gids, self.ptrs(self.host_u))
+
+        def timed(self, nsteps, host=False):
+            """(segments of this rank, device ms, per-step stats)"""
+            barrier()
+            self.jb.timer_start()
+            t0 = time.perf_counter()
+            sts = [self.step(host) for _ in range(nsteps)]
+            ms = self.jb.timer_stop()
+            torch.cuda.synchronize()
+            wall = time.perf_counter() - t0
+            barrier()
+            return sum(st["n_segments"] for st in sts), ms, wall, sts
+
+        def invariants(self, st):
+            """Quantities that must not depend on the number of ranks (streams are keyed per photon):
+            counts bit for bit, energy sums to rounding (the order of the partial sums differs)."""
+            self.read_back()
+            dv = (1.0 / self.cells) ** 3
+            keys = ("n_start", "n_sourced", "n_absorbed", "n_escaped", "n_end", "n_segments", "n_scatters",
+                    "n_block_crossings")
+            ekeys = ("e_start", "e_sourced", "e_absorbed", "e_end")
+            vals = reduce([st[k] for k in keys] + [st[k] for k in ekeys] +
+                          [float(self.host_tally.sum().item()) * dv, float(self.host_u.sum().item())])
+            out = {k: int(v) for k, v in zip(keys, vals)}
+            for k, v in zip(ekeys + ("tally_sum_times_dv", "internal_energy_sum"), vals[len(keys):]):
+                out[k] = v
+                out[k + "_hex"] = float(v).hex()
+            out["conservation_residual"] = abs(out["e_end"] - out["e_start"] - out["e_sourced"] + out["e_absorbed"]) / max(
+                abs(out["e_end"]), 1e-300)
+            return out
+
+        def close(self):
+            self.jb.close()
+            del self.dev_rho, self.dev_sie, self.host_rho, self.host_sie, self.host_tally, self.host_u
+            torch.cuda.empty_cache()
+
+    W = Workload(cells, nb, particles, args.stream, args.ddmc, args.sort_interval, args.gray_direct)
+    jb, gids, ncell = W.jb, W.gids, W.ncell
     for _ in range(args.warmup):
-        step(dev_rho, dev_sie, False)
+        W.step()
 
     # ---- timed: device-resident inputs
     sampler = ClockSampler(local_rank)
     sampler.start()
-    barrier()
     launches0 = jb.kernel_launches()
-    jb.timer_start()
-    seg = 0
-    tr_ms = 0.0
-    tr_bytes = 0.0
-    cyc_bytes = 0.0
-    last = None
-    for _ in range(args.steps):
-        st = step(dev_rho, dev_sie, False)
-        seg += st["n_segments"]
-        tr_ms += st["ms_transport"]
+    seg, ms, _, sts = W.timed(args.steps)
+    launches = jb.kernel_launches() - launches0
+    clocks = sampler.finish()
+    tr_ms = sum(st["ms_transport"] for st in sts)
+    tr_bytes = cyc_bytes = 0.0
+    for st in sts:
         n_in = st["n_start"] + st["n_sourced"] + st["n_received"]
         n_out = st["n_end"] + st["n_sent"]
         tr_bytes += 84.0 * (n_in + n_out) + 32.0 * len(gids) * ncell
         cyc_bytes += 84.0 * (n_in + n_out) + 84.0 * (st["n_start"] + st["n_sourced"]) + 40.0 * len(gids) * ncell
-        last = st
-    ms = jb.timer_stop()
-    launches = jb.kernel_launches() - launches0
-    barrier()
-    clocks = sampler.finish()
-    ms_max = reduce_max(ms)
-    seg_all = reduce_sum(seg)
+    last = sts[-1]
+    ms_max, tr_ms_max = reduce([ms, tr_ms], "max")
+    seg_all, = reduce([seg])
     value = seg_all / (ms_max * 1e-3)
-    tr_ms_max = reduce_max(tr_ms)
+    steps_identical = all(st["n_segments"] == sts[0]["n_segments"] and st["n_end"] == sts[0]["n_end"] for st in sts)
+    inv = W.invariants(last)
 
     # ---- timed: end to end through the C ABI with host buffers
     e2e = None
     if not args.no_e2e:
-        step(host_rho, host_sie, True)  # warm the host path once
-        barrier()
-        seg2 = 0
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            st = step(host_rho, host_sie, True)
-            seg2 += st["n_segments"]
-        torch.cuda.synchronize()
-        el = time.perf_counter() - t0
-        el_max = reduce_max(el)
-        seg2_all = reduce_sum(seg2)
-        nb_local = reduce_sum(len(gids))
+        W.step(host=True)  # warm the host path once
+        seg2, _, wall, _ = W.timed(args.steps, host=True)
+        el_max, = reduce([wall], "max")
+        seg2_all, nb_local = reduce([seg2, len(gids)])
         e2e = {"value": seg2_all / el_max, "unit": "segments/s",
                "h2d_bytes_per_step": int(2 * 8 * ncell * nb_local), "d2h_bytes_per_step": int(2 * 8 * ncell * nb_local),
-               "result_checksum": float(host_tally.sum().item())}
+               "result_checksum": inv["tally_sum_times_dv"],
+               "result_checksum_note": "sum over ALL ranks of energy_tally x cell volume (= census energy e_end)"}
 
-    # ---- optional: a continuing simulation (steady-state behaviour of compaction / slot order)
-    continuing = None
-    if args.continuing > 0:
-        jb.clear_particles()
-        jb.set_fields_ptr("density", gids, [dev_rho[q].data_ptr() for q in range(len(gids))])
-        jb.set_fields_ptr("sie", gids, [dev_sie[q].data_ptr() for q in range(len(gids))])
-        jb.InitializeRadiation(True)
-        jb.PostInitialization()
+    # ---- variants, timed in the same run (each a few seconds; none is the BASELINE metric's config) ----
+    def continuing_run(Wk, ncycles):
+        """one thermal initialisation followed by consecutive cycles of the same simulation (emission + feedback;
+        the population decays by ~1/3 per cycle, holes accumulate and are squeezed by occupancy)"""
+        Wk.load(False)
         barrier()
-        jb.timer_start()
-        cyc = []
-        t_now = 0.0
-        for _ in range(args.continuing):
-            st = jb.RadiationStep(t_now, dt)
-            jb.UpdateDerivedMaterial()
-            t_now += dt
+        Wk.jb.timer_start()
+        cyc, t_now = [], 0.0
+        for _ in range(ncycles):
+            st = Wk.jb.RadiationStep(t_now, Wk.dt)
+            Wk.jb.UpdateDerivedMaterial()
+            t_now += Wk.dt
             cyc.append({"n_start": st["n_start"], "n_segments": st["n_segments"], "ms_total": st["ms_total"],
                         "ms_transport": st["ms_transport"]})
-        cms = reduce_max(jb.timer_stop())
-        cseg = reduce_sum(sum(c["n_segments"] for c in cyc))
-        continuing = {"cycles": args.continuing, "value": cseg / (cms * 1e-3), "unit": "segments/s", "ms": cms,
-                      "per_cycle_rank0": cyc}
+        cms, = reduce([Wk.jb.timer_stop()], "max")
+        cseg, = reduce([sum(c["n_segments"] for c in cyc)])
+        return {"cycles": ncycles, "value": cseg / (cms * 1e-3), "unit": "segments/s", "ms": cms, "per_cycle_rank0": cyc}
+
+    def variant(name, fn):
+        try:
+            return fn()
+        except Exception as exc:  # noqa: BLE001
+            return {"error": f"{type(exc).__name__}: {exc}"}
+
+    variants = {}
+    plain = not (args.stream or args.ddmc)
+    if args.variants and plain:
+        variants["continuing"] = variant("continuing", lambda: dict(
+            continuing_run(W, 8), workload=f"{cells}^3: thermal initialisation + 8 consecutive cycles, unsorted pool"))
+        if args.sort_interval == 0:
+            def sorted_run():
+                Ws = W
+                Ws.jb.set_sort_interval(1)
+                try:
+                    return dict(continuing_run(Ws, 8),
+                                workload=f"{cells}^3: same, pool sorted by (meshblock, cell) after every cycle")
+                finally:
+                    Ws.jb.set_sort_interval(0)
+            variants["continuing_sorted"] = variant("continuing_sorted", sorted_run)
+    continuing = None
+    if args.continuing > 0:
+        continuing = continuing_run(W, args.continuing)
 
     peaks = {}
     try:
@@ -400,41 +490,76 @@ def main():
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    achieved = tr_bytes / (tr_ms * 1e-3) / 1e9 if tr_ms > 0 else 0.0
-    # DRAM traffic of the kernel: measured once with ncu on the 64^3 twin (profiles/r01_traffic.json) as a ratio to
-    # the algorithmic bytes of that launch; reported here scaled to this run's launch (None if the file is absent)
-    traffic, traffic_src, ncu_pipe = None, None, {}
-    try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
-        if not args.stream and not args.ddmc:
-            traffic = tj["ratio"] * tr_bytes / max(args.steps, 1)
-            traffic_src = f"ncu at {tj['cells']}^3: dram bytes / algorithmic bytes = {tj['ratio']}, scaled to this launch"
-            ncu_pipe = {"fp64_pipe_pct": tj.get("fp64_pipe_pct"), "issue_active_pct": tj.get("issue_active_pct")}
-    except Exception:
-        pass
-    roofline = {"bound": "hbm", "kernel": "k_transport<ddmc>" if args.ddmc else "k_transport_imc", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "ncu": ncu_pipe,
-                "note": "8.3 segments per photon make this kernel FP64-issue bound (~220 FP64 ops per segment against "
-                        "~17 algorithmic bytes); bench.py --stream measures the same kernel in the bandwidth-bound regime",
-                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
-                "bytes_per_launch": tr_bytes / max(args.steps, 1), "ms_per_launch": tr_ms / max(args.steps, 1),
-                "bytes_per_segment": tr_bytes / max(seg, 1),
-                "whole_cycle_GBps": cyc_bytes / (ms * 1e-3) / 1e9,
-                "segments_per_photon": seg / max(args.steps * (last["n_start"] + last["n_sourced"]), 1)}
-
-    # second roofline (SURVEY 8d honesty note): FP64 pipe. Peak = DFMA chain kernel measured now on this GPU;
-    # flops per segment = DFMA x2 + DMUL + DADD of the kernel's main body, counted by ncu (profiles/r01_traffic.json)
-    fp64 = None
+    fpeak_err, fpeak = None, None
     try:
         fpeak = jb.measure_fp64_peak()
-        fps = float(tj.get("fp64_flops_per_segment", 317.0)) if not args.stream else 317.0
-        fach = (seg / (tr_ms * 1e-3)) * fps / 1e12 if tr_ms > 0 else 0.0
-        fp64 = {"bound": "fp64", "peak": fpeak, "unit": "TFLOP/s", "peak_source": "k_fp64_chain measured in this run",
-                "flops_per_segment": fps, "achieved": fach, "frac": fach / fpeak if fpeak > 0 else None,
-                "pipe_active_pct_ncu": ncu_pipe.get("fp64_pipe_pct")}
     except Exception as exc:  # noqa: BLE001
-        fp64 = {"error": str(exc)}
-    roofline["fp64"] = fp64
+        fpeak_err = str(exc)
+    W.close()
+
+    if args.variants and plain:
+        def small(stream, ddmc, cells_v, label):
+            def run():
+                pv = int(round(1.0e9 * (cells_v / 256.0) ** 3))
+                Wv = Workload(cells_v, min(nb, cells_v), pv, stream=stream, ddmc=ddmc)
+                try:
+                    Wv.step()
+                    sg, vms, _, vsts = Wv.timed(2)
+                    vms_max, vtr = reduce([vms, sum(x["ms_transport"] for x in vsts)], "max")
+                    sg_all, = reduce([sg])
+                    l = vsts[-1]
+                    return {"workload": label.format(cells=cells_v, photons=pv), "value": sg_all / (vms_max * 1e-3),
+                            "unit": "segments/s", "ms_per_step": vms_max / 2, "transport_ms_per_step": vtr / 2,
+                            "segments_per_photon": l["n_segments"] / max(l["n_start"] + l["n_sourced"], 1),
+                            "n_ddmc_segments": l["n_ddmc_segments"]}
+                finally:
+                    Wv.close()
+            return run
+        variants["ddmc"] = variant("ddmc", small(False, True, min(cells, 128),
+                                   "C5-ddmc {cells}^3 / {photons} photons: sigma*dx = 8, use_ddmc, tau_ddmc = 5 (k_transport_hybrid)"))
+        variants["stream"] = variant("stream", small(True, False, cells,
+                                     "C5-stream {cells}^3 / {photons} photons: dt = dx/(2c), kappa = sigma = 0 (bandwidth-bound limit)"))
+
+    achieved = tr_bytes / (tr_ms * 1e-3) / 1e9 if tr_ms > 0 else 0.0
+    # DRAM traffic of the kernel: measured once with ncu on the 64^3 twin (profiles/*_traffic.json) as a ratio to
+    # the algorithmic bytes of that launch; reported here scaled to this run's launch (None if the file is absent)
+    traffic, traffic_src, ncu_pipe, tj = None, None, {}, {}
+    for tname in ("r02_traffic.json", "r01_traffic.json"):
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", tname)))
+            break
+        except Exception:
+            continue
+    if tj and plain:
+        traffic = tj["ratio"] * tr_bytes / max(args.steps, 1)
+        traffic_src = f"ncu at {tj['cells']}^3 ({tname}): dram bytes / algorithmic bytes = {tj['ratio']}, scaled to this launch"
+        ncu_pipe = {"fp64_pipe_pct": tj.get("fp64_pipe_pct"), "issue_active_pct": tj.get("issue_active_pct"),
+                    "kernel": tj.get("kernel")}
+    fps = float(tj.get("fp64_flops_per_segment", 324.0)) if tj else 324.0
+    spp = seg / max(args.steps * (last["n_start"] + last["n_sourced"]), 1)
+    kernel_name = "k_transport_hybrid" if args.ddmc else os.environ.get("JB_TRANSPORT_VARIANT", "2") == "1" and "k_transport_imc" or "k_transport_pool"
+    roofline = {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "ncu": ncu_pipe,
+                "note": f"{spp:.1f} segments per photon make this kernel FP64-issue / latency bound ({fps:.0f} FP64 flop per "
+                        f"segment against {tr_bytes / max(seg, 1):.0f} algorithmic bytes); variants.stream measures the same "
+                        "kernel in the bandwidth-bound regime",
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
+                "bytes_per_launch": tr_bytes / max(args.steps, 1), "ms_per_launch": tr_ms / max(args.steps, 1),
+                "bytes_per_launch_formula": "84 B x (photons in + photons out) + 32 B x cells (the CellProps record the "
+                                            "kernel reads; SURVEY 8d's 40 B x cells is per CYCLE and is used in whole_cycle_GBps)",
+                "bytes_per_segment": tr_bytes / max(seg, 1),
+                "whole_cycle_GBps": cyc_bytes / (ms * 1e-3) / 1e9,
+                "segments_per_photon": spp}
+
+    # second roofline (SURVEY 8d honesty note): FP64 pipe. Peak = DFMA chain kernel measured now on this GPU;
+    # flops per segment = DFMA x2 + DMUL + DADD of the kernel's main body, counted by ncu (profiles/*_traffic.json)
+    if fpeak:
+        fach = (seg / (tr_ms * 1e-3)) * fps / 1e12 if tr_ms > 0 else 0.0
+        roofline["fp64"] = {"bound": "fp64", "peak": fpeak, "unit": "TFLOP/s", "peak_source": "k_fp64_chain measured in this run",
+                            "flops_per_segment": fps, "achieved": fach, "frac": fach / fpeak if fpeak > 0 else None,
+                            "pipe_active_pct_ncu": ncu_pipe.get("fp64_pipe_pct")}
+    else:
+        roofline["fp64"] = {"error": fpeak_err}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -442,7 +567,7 @@ def main():
         cpu_particles = int(round(particles * (cpu_cells / cells) ** 3))
         v, cms, info = cpu_arm(cpu_cells, nb, cpu_particles, 1, 1)
         cpu = {"value": v, "unit": "segments/s", "cores": info["cores"], "kind": info["kind"], "sample": info["sample"],
-               "ms_per_step": cms}
+               "ms_per_step": cms, "twin": {k: info[k] for k in ("cells", "photons_per_step", "shrunk_to_fit_time_budget")}}
 
     if rank == 0:
         line = {"metric": "IMC particle-segments/sec", "value": value, "unit": "segments/s", "n_gpus": world,
@@ -450,9 +575,13 @@ def main():
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "config": config, "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
                 "roofline": roofline, "cpu_baseline": cpu,
-                "transport_ms_per_step": tr_ms_max / max(args.steps, 1), "continuing": continuing,
-                "last_step": {k: last[k] for k in ("n_start", "n_sourced", "n_absorbed", "n_end", "n_sent", "n_received",
-                                                    "n_segments", "n_scatters", "n_block_crossings", "n_iterations")}}
+                "transport_ms_per_step": tr_ms_max / max(args.steps, 1),
+                "invariants": dict(inv, steps_identical=steps_identical,
+                                   note="all-reduced over the ranks; every step sources the same photons (jb_reset_streams), "
+                                        "so these are equal for every N, K and W"),
+                "variants": variants or None, "continuing": continuing,
+                "last_step_rank0": {k: last[k] for k in ("n_start", "n_sourced", "n_absorbed", "n_end", "n_sent", "n_received",
+                                                          "n_segments", "n_scatters", "n_block_crossings", "n_iterations")}}
         print(json.dumps(line))
     if world > 1:
         dist.barrier()

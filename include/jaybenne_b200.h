@@ -139,7 +139,7 @@ typedef struct jb_cycle_stats {
   int64_t n_scatters;
   int64_t n_ddmc_segments;
   int32_t n_iterations;   /* transport/exchange iterations                               */
-  int32_t reserved;
+  int32_t n_bface_resampled; /* photons SampleDDMCBlockFace spread over a fine face (SampleFace2D/3D) */
   double e_start;         /* sum of weights at cycle start                               */
   double e_sourced;
   double e_absorbed;
@@ -256,6 +256,12 @@ jb_status jb_num_particles(jb_ctx *ctx, int64_t *n_local);
 jb_status jb_get_particles(jb_ctx *ctx, const jb_particles *dst, int64_t capacity, int64_t *n);
 /* replaces the local swarm with `n` host particles (Parthenon adapter: swarm -> ctx) */
 jb_status jb_set_particles(jb_ctx *ctx, const jb_particles *src, int64_t n);
+/* restart the sourcing-call counter that keys the per-photon Philox streams (birth index, birth gid,
+ * source call): a run repeated on the same inputs after this call reproduces the same photons. The
+ * reference's pool generator has no counterpart (its streams depend on the thread schedule). */
+jb_status jb_reset_streams(jb_ctx *ctx);
+/* change jb_config::sort_interval of a live context (0 = never sort the pool by (meshblock, cell)) */
+jb_status jb_set_sort_interval(jb_ctx *ctx, int32_t every_n_cycles);
 /* cumulative stats since the last jb_radiation_step / jb_stats_begin began */
 jb_status jb_get_stats(jb_ctx *ctx, jb_cycle_stats *stats);
 /* zero the counters and record n_start / e_start: for hosts that drive the individual

@@ -13,6 +13,7 @@ import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libjaybenne_b200.so")
+HOST_LIB_PATH = os.path.join(HERE, "libjb_host.so")
 
 # ---- enums ---------------------------------------------------------------------------
 JB_OK, JB_ERR_INVALID, JB_ERR_CUDA, JB_ERR_CAPACITY, JB_ERR_STATE = 0, 1, 2, 3, 4
@@ -78,7 +79,7 @@ class jb_cycle_stats(C.Structure):
         ("n_start", C.c_int64), ("n_sourced", C.c_int64), ("n_absorbed", C.c_int64), ("n_escaped", C.c_int64),
         ("n_end", C.c_int64), ("n_sent", C.c_int64), ("n_received", C.c_int64), ("n_block_crossings", C.c_int64),
         ("n_segments", C.c_int64), ("n_scatters", C.c_int64), ("n_ddmc_segments", C.c_int64),
-        ("n_iterations", C.c_int32), ("reserved", C.c_int32), ("e_start", C.c_double), ("e_sourced", C.c_double),
+        ("n_iterations", C.c_int32), ("n_bface_resampled", C.c_int32), ("e_start", C.c_double), ("e_sourced", C.c_double),
         ("e_absorbed", C.c_double), ("e_escaped", C.c_double), ("e_end", C.c_double),
         ("ms_transport", C.c_double), ("ms_total", C.c_double),
     ]
@@ -136,6 +137,7 @@ COMPUTE_API = {
     "num_particles": (C.c_int, [ctx_p, C.POINTER(C.c_int64)]),
     "get_particles": (C.c_int, [ctx_p, C.POINTER(jb_particles), C.c_int64, C.POINTER(C.c_int64)]),
     "set_particles": (C.c_int, [ctx_p, C.POINTER(jb_particles), C.c_int64]),
+    "reset_streams": (C.c_int, [ctx_p]),
     "get_stats": (C.c_int, [ctx_p, C.POINTER(jb_cycle_stats)]),
     "stats_begin": (C.c_int, [ctx_p]),
     "event_log_enable": (C.c_int, [ctx_p, C.c_int64]),
@@ -161,6 +163,7 @@ DEVICE_API = {
     "exchange_take_device": (C.c_int, [ctx_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
     "exchange_give_device": (C.c_int, [ctx_p, C.c_void_p, C.c_int64]),
     "exchange_clear": (C.c_int, [ctx_p]),
+    "set_sort_interval": (C.c_int, [ctx_p, C.c_int32]),
     "set_remote_field": (C.c_int, [ctx_p, C.c_int32, C.c_int32, C.c_void_p]),
     "set_fields": (C.c_int, [ctx_p, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_void_p)]),
     "get_fields": (C.c_int, [ctx_p, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_void_p)]),
@@ -207,6 +210,21 @@ def load_library():
 
 def device_api():
     return Api(load_library(), "jb_", (COMPUTE_API, DEVICE_API, DECK_API))
+
+
+_HOST = None
+
+
+def host_api():
+    """The deck reader / mesh-table builder (csrc/host/deck.cpp) as its own host-only library: parsing an input
+    deck must not need (or map) the CUDA library."""
+    global _HOST
+    if _HOST is None:
+        if not os.path.exists(HOST_LIB_PATH):
+            raise ImportError(f"{HOST_LIB_PATH} is missing: build it with make -C jaybenne_b200/csrc")
+        lib = C.CDLL(HOST_LIB_PATH)
+        _HOST = Api(lib, "jb_", (DECK_API, {"config_default": DEVICE_API["config_default"]}))
+    return _HOST
 
 
 def declared_symbols():

@@ -496,42 +496,6 @@ __device__ __forceinline__ void ddmc_step(Rng &rng, const double t_end, const Ce
   }
 }
 
-// SampleFace2D / SampleFace3D (sample_ddmc_bface.cpp:24-78): pick one of the fine faces
-// that share the coarse face the photon came through, in proportion to their leakage
-// probabilities, and spread the photon over the chosen fine face.
-__device__ __forceinline__ void sample_face_2d(const int i_l, const double dx, const double P_l, const double P_u,
-                                               Rng &rng, int &i, double &x) {
-  const int i_u = i_l + 1;
-  const double xi = (P_l + P_u) * rng.drand();
-  if (xi < P_l) {
-    x -= dx * rng.drand();
-    i = i_l;
-  } else {
-    x += dx * rng.drand();
-    i = i_u;
-  }
-}
-__device__ __forceinline__ void sample_face_3d(const int i1_l, const int i2_l, const double dx1, const double dx2,
-                                               const double P_ll, const double P_lu, const double P_ul,
-                                               const double P_uu, Rng &rng, int &i1, int &i2, double &x1,
-                                               double &x2) {
-  const int i1_u = i1_l + 1, i2_u = i2_l + 1;
-  const double xi = (P_ll + P_lu + P_ul + P_uu) * rng.drand();
-  if (xi < P_ll) {
-    x1 -= dx1 * rng.drand(); i1 = i1_l;
-    x2 -= dx2 * rng.drand(); i2 = i2_l;
-  } else if (xi < P_ll + P_lu) {
-    x1 += dx1 * rng.drand(); i1 = i1_u;
-    x2 -= dx2 * rng.drand(); i2 = i2_l;
-  } else if (xi < P_ll + P_lu + P_ul) {
-    x1 -= dx1 * rng.drand(); i1 = i1_l;
-    x2 += dx2 * rng.drand(); i2 = i2_u;
-  } else {
-    x1 += dx1 * rng.drand(); i1 = i1_u;
-    x2 += dx2 * rng.drand(); i2 = i2_u;
-  }
-}
-
 }  // namespace jbd
 
 #endif  // JAYBENNE_B200_JB_DEVICE_CUH_

@@ -553,105 +553,103 @@ __device__ __forceinline__ void log_event(const StepParams &P, const uint4 &id, 
   P.log.ev[slot] = e;
 }
 
-// SampleDDMCBlockFace for one photon (sample_ddmc_bface.cpp:81-427). Face-probability
-// reads one index outside the block are clamped (the reference reads exchanged ghosts).
+// SampleDDMCBlockFace for one photon (sample_ddmc_bface.cpp:81-427): a photon that a DDMC leak carried out
+// of a COARSER block arrives with zero velocity, 2 eps_ddmc fine cell widths inside this block and at the
+// coarse cell's centre in the transverse directions, i.e. on an edge (2D) or a vertex (3D) between fine
+// cells. It gets an inward cosine-law direction and one of the 2 / 4 fine faces that tile the coarse face
+// it came through, drawn in proportion to their leakage probabilities, and is spread over that face.
+// One evaluation parametrised by the face's axis replaces the reference's per-face copies: `a` is the
+// normal axis, (t1, t2) the transverse axes in increasing order — the argument orders of the reference's
+// SampleFace2D / SampleFace3D call sites — and draws, operands and operation order are the reference's.
+// The reference reads the probabilities through ghost-inclusive face indices; on a 2:1 mesh the pair of
+// fine cells under a coarse cell never straddles a block edge, so an index outside the block cannot occur:
+// it is counted (DStats::n_bface_ghost, the step fails) instead of being clamped silently.
 template <int NDIM>
 __device__ void bface_sample(const StepParams &P, const BlkReg &B, Photon &p, Rng &rng) {
   if (NDIM < 2) return;
   const DMesh &m = P.mesh;
-  constexpr bool three_d = NDIM > 2;
   const double vv = P.cl.c_code;
   const double eps = EPS10;
   if (!(p.vx * p.vx + p.vy * p.vy + p.vz * p.vz < eps * vv * vv)) return;
-  const int n1 = m.nxb[0], n2 = m.nxb[1], n3 = m.nxb[2];
-  const double *fp0 = P.f.fp[0] + (size_t)B.lb * P.f.nface[0];
-  const double *fp1 = P.f.fp[1] + (size_t)B.lb * P.f.nface[1];
-  const double *fp2 = three_d ? P.f.fp[2] + (size_t)B.lb * P.f.nface[2] : nullptr;
-  auto clampi = [](int v, int lo, int hi) { return min(max(v, lo), hi); };
-  auto F1 = [&](int k, int j, int i) {
-    return fp0[((size_t)clampi(k, 0, n3 - 1) * n2 + clampi(j, 0, n2 - 1)) * (n1 + 1) + clampi(i, 0, n1)];
-  };
-  auto F2 = [&](int k, int j, int i) {
-    return fp1[((size_t)clampi(k, 0, n3 - 1) * (n2 + 1) + clampi(j, 0, n2)) * n1 + clampi(i, 0, n1 - 1)];
-  };
-  auto F3 = [&](int k, int j, int i) {
-    return fp2[((size_t)clampi(k, 0, n3) * n2 + clampi(j, 0, n2 - 1)) * n1 + clampi(i, 0, n1 - 1)];
-  };
-  int &ip = p.ip, &jp = p.jp, &kp = p.kp;
-  double &x = p.x, &y = p.y, &z = p.z;
-  xtoijk<NDIM>(B, p, ip, jp, kp);
-  const double dx_i = B.dx[0], dy_j = B.dx[1], dz_k = B.dx[2];
-  const double x_i = xc(B, m.ng[0], 0, ip) - 0.5 * dx_i;
-  const double y_j = xc(B, m.ng[1], 1, jp) - 0.5 * dy_j;
-  const double z_k = xc(B, m.ng[2], 2, kp) - 0.5 * dz_k;
-  const bool at_block_x_min = fuzzy_eq(x, B.xmin[0] + 2.0 * EPS_DDMC * dx_i, dx_i, eps);
-  const bool at_block_x_max = fuzzy_eq(x, B.xmax[0] - 2.0 * EPS_DDMC * dx_i, dx_i, eps);
-  const bool at_block_y_min = fuzzy_eq(y, B.xmin[1] + 2.0 * EPS_DDMC * dy_j, dy_j, eps);
-  const bool at_block_y_max = fuzzy_eq(y, B.xmax[1] - 2.0 * EPS_DDMC * dy_j, dy_j, eps);
-  const bool at_block_z_min = three_d && fuzzy_eq(z, B.xmin[2] + 2.0 * EPS_DDMC * dz_k, dz_k, eps);
-  const bool at_block_z_max = three_d && fuzzy_eq(z, B.xmax[2] - 2.0 * EPS_DDMC * dz_k, dz_k, eps);
-  if (at_block_x_min || at_block_x_max) {
-    const double dir_sgn = at_block_x_min ? 1.0 : -1.0;
-    face_iso_dir(dir_sgn * vv, rng, p.vx, p.vy, p.vz);
-    const int ip_b = at_block_x_min ? ip : ip + 1;
-    const bool at_y_edge_u = fuzzy_eq(y, y_j, dy_j, eps);
-    const bool at_y_edge_l = fuzzy_eq(y, y_j + dy_j, dy_j, eps);
-    if (!three_d) {
-      if (at_y_edge_u || at_y_edge_l) {
-        const int jp_u = at_y_edge_u ? jp : jp + 1;
-        const int jp_l = at_y_edge_u ? jp - 1 : jp;
-        sample_face_2d(jp_l, dy_j, F1(kp, jp_l, ip_b), F1(kp, jp_u, ip_b), rng, jp, y);
-      }
-    } else {
-      const bool at_z_edge_u = fuzzy_eq(z, z_k, dz_k, eps);
-      const bool at_z_edge_l = fuzzy_eq(z, z_k + dz_k, dz_k, eps);
-      if ((at_y_edge_u || at_y_edge_l) && (at_z_edge_u || at_z_edge_l)) {
-        const int jp_u = at_y_edge_u ? jp : jp + 1, jp_l = at_y_edge_u ? jp - 1 : jp;
-        const int kp_u = at_z_edge_u ? kp : kp + 1, kp_l = at_z_edge_u ? kp - 1 : kp;
-        const double Px_uu = F1(kp_u, jp_u, ip_b), Px_ul = F1(kp_u, jp_l, ip_b);
-        const double Px_lu = F1(kp_l, jp_u, ip_b), Px_ll = F1(kp_l, jp_l, ip_b);
-        sample_face_3d(jp_l, kp_l, dy_j, dz_k, Px_ll, Px_lu, Px_ul, Px_uu, rng, jp, kp, y, z);
-      }
-    }
-  } else if (at_block_y_min || at_block_y_max) {
-    const double dir_sgn = at_block_y_min ? 1.0 : -1.0;
-    face_iso_dir(dir_sgn * vv, rng, p.vy, p.vz, p.vx);
-    const int jp_b = at_block_y_min ? jp : jp + 1;
-    const bool at_x_edge_u = fuzzy_eq(x, x_i, dx_i, eps);
-    const bool at_x_edge_l = fuzzy_eq(x, x_i + dx_i, dx_i, eps);
-    if (!three_d) {
-      if (at_x_edge_u || at_x_edge_l) {
-        const int ip_u = at_x_edge_u ? ip : ip + 1;
-        const int ip_l = at_x_edge_u ? ip - 1 : ip;
-        sample_face_2d(ip_l, dx_i, F2(kp, jp_b, ip_l), F2(kp, jp_b, ip_u), rng, ip, x);
-      }
-    } else {
-      const bool at_z_edge_u = fuzzy_eq(z, z_k, dz_k, eps);
-      const bool at_z_edge_l = fuzzy_eq(z, z_k + dz_k, dz_k, eps);
-      if ((at_z_edge_u || at_z_edge_l) && (at_x_edge_u || at_x_edge_l)) {
-        const int kp_u = at_z_edge_u ? kp : kp + 1, kp_l = at_z_edge_u ? kp - 1 : kp;
-        const int ip_u = at_x_edge_u ? ip : ip + 1, ip_l = at_x_edge_u ? ip - 1 : ip;
-        const double Py_uu = F2(kp_u, jp_b, ip_u), Py_ul = F2(kp_u, jp_b, ip_l);
-        const double Py_lu = F2(kp_l, jp_b, ip_u), Py_ll = F2(kp_l, jp_b, ip_l);
-        sample_face_3d(ip_l, kp_l, dx_i, dz_k, Py_ll, Py_lu, Py_ul, Py_uu, rng, ip, kp, x, z);
-      }
-    }
-  } else if (at_block_z_min || at_block_z_max) {
-    const double dir_sgn = at_block_z_min ? 1.0 : -1.0;
-    face_iso_dir(dir_sgn * vv, rng, p.vz, p.vx, p.vy);
-    const int kp_b = at_block_z_min ? kp : kp + 1;
-    const bool at_x_edge_u = fuzzy_eq(x, x_i, dx_i, eps);
-    const bool at_x_edge_l = fuzzy_eq(x, x_i + dx_i, dx_i, eps);
-    const bool at_y_edge_u = fuzzy_eq(y, y_j, dy_j, eps);
-    const bool at_y_edge_l = fuzzy_eq(y, y_j + dy_j, dy_j, eps);
-    if ((at_x_edge_u || at_x_edge_l) && (at_y_edge_u || at_y_edge_l)) {
-      const int ip_u = at_x_edge_u ? ip : ip + 1, ip_l = at_x_edge_u ? ip - 1 : ip;
-      const int jp_u = at_y_edge_u ? jp : jp + 1, jp_l = at_y_edge_u ? jp - 1 : jp;
-      const double Pz_uu = F3(kp_b, jp_u, ip_u), Pz_ul = F3(kp_b, jp_u, ip_l);
-      const double Pz_lu = F3(kp_b, jp_l, ip_u), Pz_ll = F3(kp_b, jp_l, ip_l);
-      sample_face_3d(ip_l, jp_l, dx_i, dy_j, Pz_ll, Pz_lu, Pz_ul, Pz_uu, rng, ip, jp, x, y);
+  xtoijk<NDIM>(B, p, p.ip, p.jp, p.kp);
+  double pos[3] = {p.x, p.y, p.z};
+  int ijk[3] = {p.ip, p.jp, p.kp};
+  // which block face (x before y before z, lower before upper, as the reference's if / else-if chain)
+  int a = -1;
+  bool at_min = false;
+#pragma unroll
+  for (int d = NDIM - 1; d >= 0; --d) {
+    const bool lo = fuzzy_eq(pos[d], B.xmin[d] + 2.0 * EPS_DDMC * B.dx[d], B.dx[d], eps);
+    const bool hi = fuzzy_eq(pos[d], B.xmax[d] - 2.0 * EPS_DDMC * B.dx[d], B.dx[d], eps);
+    if (lo || hi) {
+      a = d;
+      at_min = lo;
     }
   }
+  if (a < 0) return;
+  {
+    double v1, v2, v3;
+    face_iso_dir(at_min ? vv : -vv, rng, v1, v2, v3);
+    unpermute_dir(a, v1, v2, v3, p.vx, p.vy, p.vz);
+  }
+  const int t1 = a == 0 ? 1 : 0, t2 = a == 2 ? 1 : 2;
+  // is the photon on the lower (`up`: it then belongs to the upper candidate) or the upper edge of its cell?
+  bool on_edge[3] = {false, false, false};
+  int i_l[3] = {ijk[0], ijk[1], ijk[2]};
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int t = q == 0 ? t1 : t2;
+    if (t >= NDIM) continue;
+    const double lo_t = xc(B, m.ng[t], t, ijk[t]) - 0.5 * B.dx[t];
+    const bool edge_u = fuzzy_eq(pos[t], lo_t, B.dx[t], eps);
+    const bool edge_l = fuzzy_eq(pos[t], lo_t + B.dx[t], B.dx[t], eps);
+    on_edge[t] = edge_u || edge_l;
+    i_l[t] = edge_u ? ijk[t] - 1 : ijk[t];
+  }
+  const int nx[3] = {m.nxb[0], m.nxb[1], m.nxb[2]};
+  const double *fpa = P.f.fp[a] + (size_t)B.lb * P.f.nface[a];
+  int f[3] = {ijk[0], ijk[1], ijk[2]};
+  f[a] = at_min ? ijk[a] : ijk[a] + 1;
+  auto prob = [&](int o1, int o2) {  // face (i_l[t1] + o1, i_l[t2] + o2) of the block face
+    int g[3] = {f[0], f[1], f[2]};
+    g[t1] = i_l[t1] + o1;
+    if (NDIM > 2) g[t2] = i_l[t2] + o2;
+    bool ghost = false;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      const int hi = nx[d] - 1 + (d == a ? 1 : 0);
+      if (g[d] < 0 || g[d] > hi) {
+        ghost = true;
+        g[d] = min(max(g[d], 0), hi);
+      }
+    }
+    if (ghost) atomicAdd(&P.stats->n_bface_ghost, 1ull);
+    return fpa[((size_t)g[2] * (nx[1] + (a == 1 ? 1 : 0)) + g[1]) * (nx[0] + (a == 0 ? 1 : 0)) + g[0]];
+  };
+  if (NDIM == 2) {
+    if (!on_edge[t1]) return;  // SampleFace2D (sample_ddmc_bface.cpp:24-39)
+    const double P_l = prob(0, 0), P_u = prob(1, 0);
+    const double xi = (P_l + P_u) * rng.drand();
+    const int up = xi < P_l ? 0 : 1;
+    const double r = B.dx[t1] * rng.drand();
+    pos[t1] = up ? pos[t1] + r : pos[t1] - r;
+    ijk[t1] = i_l[t1] + up;
+  } else {
+    if (!(on_edge[t1] && on_edge[t2])) return;  // SampleFace3D (sample_ddmc_bface.cpp:41-78)
+    const double P_ll = prob(0, 0), P_lu = prob(1, 0), P_ul = prob(0, 1), P_uu = prob(1, 1);
+    const double xi = (P_ll + P_lu + P_ul + P_uu) * rng.drand();
+    const int sel = xi < P_ll ? 0 : (xi < P_ll + P_lu ? 1 : (xi < P_ll + P_lu + P_ul ? 2 : 3));
+    const int up1 = sel & 1, up2 = sel >> 1;
+    const double r1 = B.dx[t1] * rng.drand();
+    pos[t1] = up1 ? pos[t1] + r1 : pos[t1] - r1;
+    ijk[t1] = i_l[t1] + up1;
+    const double r2 = B.dx[t2] * rng.drand();
+    pos[t2] = up2 ? pos[t2] + r2 : pos[t2] - r2;
+    ijk[t2] = i_l[t2] + up2;
+  }
+  atomicAdd(&P.stats->n_bface, 1ull);
+  p.x = pos[0]; p.y = pos[1]; p.z = pos[2];
+  p.ip = ijk[0]; p.jp = ijk[1]; p.kp = ijk[2];
 }
 
 // The history kernel. One thread owns one photon from its current state to the first of:
@@ -841,13 +839,24 @@ static void launch_transport_nd(const StepParams &P, long long first, long long 
 }
 
 #include "jb_transport_imc.cuh"
+#include "jb_transport_pool.cuh"
 #include "jb_transport_ddmc.cuh"
 
 void launch_transport(const StepParams &P, long long first, long long n, double t_start, double dt,
                       cudaStream_t st) {
   if (n <= 0) return;
   const bool dd = P.use_ddmc != 0;
-  if (!dd && P.log.cap <= 0 && g_tuning.variant == 1) {
+  if (!dd && P.log.cap <= 0 && g_tuning.variant == 2) {
+    bool ok;
+    switch (P.mesh.ndim) {
+      case 1: ok = launch_transport_pool<1>(P, first, n, t_start, dt, st); break;
+      case 2: ok = launch_transport_pool<2>(P, first, n, t_start, dt, st); break;
+      default: ok = launch_transport_pool<3>(P, first, n, t_start, dt, st); break;
+    }
+    if (ok) return;
+  }
+  // 32-bit slot offsets inside the persistent kernels: longer ranges take the thread-per-photon kernel
+  if (!dd && P.log.cap <= 0 && g_tuning.variant >= 1 && n < 0xffffffffLL) {
     switch (P.mesh.ndim) {
       case 1: launch_transport_imc<1>(P, first, n, t_start, dt, st); break;
       case 2: launch_transport_imc<2>(P, first, n, t_start, dt, st); break;
@@ -855,7 +864,7 @@ void launch_transport(const StepParams &P, long long first, long long n, double 
     }
     return;
   }
-  if (dd && g_tuning.variant == 1) {  // hybrid IMC / DDMC: persistent warps with lane refill
+  if (dd && g_tuning.variant >= 1) {  // hybrid IMC / DDMC: persistent warps with lane refill
     switch (P.mesh.ndim) {
       case 1: launch_transport_hybrid<1>(P, first, n, t_start, dt, st); break;
       case 2: launch_transport_hybrid<2>(P, first, n, t_start, dt, st); break;

@@ -94,6 +94,9 @@ struct DStats {
   unsigned long long n_sourced, n_absorbed, n_escaped, n_sent, n_received, n_crossings;
   unsigned long long n_segments, n_scatters, n_ddmc, n_unfinished, n_error, n_dead;
   unsigned long long n_events, n_overflow;
+  unsigned long long n_bface;        // photons spread over a fine face by SampleFace2D / SampleFace3D
+  unsigned long long n_bface_ghost;  // block-face resampling indexed a face probability outside the block
+  unsigned long long n_validate;  // VALIDATE builds: index / division cross-checks that disagreed
   double e_sourced, e_absorbed, e_escaped;
 };
 
@@ -140,12 +143,14 @@ void launch_transport(const StepParams &P, long long first, long long n, double 
                       cudaStream_t st);
 // knobs of the persistent IMC kernel (jb_lib.cu reads them from the environment once)
 struct TransportTuning {
-  int variant;      // 0 = thread-per-photon history kernel, 1 = persistent warps with lane refill
+  int variant;      // 0 = thread-per-photon history kernel, 1 = persistent warps with lane refill (v9),
+                    // 2 = warp-private photon pools in shared memory, phase by phase (v10, IMC only; default)
   int ctas_per_sm;  // CTAs of 128 threads per SM: 4, 6 or 8 (default)
   int refill_min;   // refill when at least this many lanes of a warp are idle
   int validate;     // 1: cross-check the face-crossing index update against Xtoijk (n_error)
 };
 void set_transport_tuning(const TransportTuning &t);
+void set_pool_tuning(int slots, int refill_min, int ready_low);
 void launch_pack_props(const StepParams &P, cudaStream_t st);
 // folds ebins[kind] into *dst (dst = &stats->e_* or the census scratch)
 void launch_fold_bins(const StepParams &P, int kind, double *dst, cudaStream_t st);

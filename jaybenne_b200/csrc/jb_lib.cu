@@ -348,12 +348,19 @@ jb_status jb_create(const jb_config *cfg, jb_ctx **out) {
   cudaMemset(c->d_ebins, 0, sizeof(double) * EB_KINDS * EBINS);
   // kernel tuning knobs (diagnostics / A-B measurements; defaults are the shipped configuration)
   {
-    TransportTuning t = {1, 8, 4, 0};
+    TransportTuning t = {2, 8, 4, 0};
     if (const char *v = getenv("JB_TRANSPORT_VARIANT")) t.variant = atoi(v);
     if (const char *v = getenv("JB_IMC_CTAS_PER_SM")) t.ctas_per_sm = atoi(v);
     if (const char *v = getenv("JB_IMC_REFILL_MIN")) t.refill_min = std::max(1, std::min(32, atoi(v)));
     if (const char *v = getenv("JB_IMC_VALIDATE")) t.validate = atoi(v);
     set_transport_tuning(t);
+    {
+      int ps = 64, prf = 24, prl = 32;
+      if (const char *v = getenv("JB_POOL_SLOTS")) ps = atoi(v);
+      if (const char *v = getenv("JB_POOL_REFILL_MIN")) prf = atoi(v);
+      if (const char *v = getenv("JB_POOL_READY_LOW")) prl = atoi(v);
+      set_pool_tuning(ps, prf, prl);
+    }
   }
   *out = c;
   return JB_OK;
@@ -785,6 +792,7 @@ static void fold_stats(jb_ctx *c) {
   c->stats.n_segments = (int64_t)h.n_segments;
   c->stats.n_scatters = (int64_t)h.n_scatters;
   c->stats.n_ddmc_segments = (int64_t)h.n_ddmc;
+  c->stats.n_bface_resampled = (int32_t)h.n_bface;
   c->stats.e_sourced = h.e_sourced;
   c->stats.e_absorbed = h.e_absorbed;
   c->stats.e_escaped = h.e_escaped;
@@ -792,6 +800,11 @@ static void fold_stats(jb_ctx *c) {
 static jb_status check_device_errors(jb_ctx *c) {
   if (c->h_stats->n_error)
     return fail(c, JB_ERR_STATE, "particle left the domain without a boundary condition");
+  if (c->h_stats->n_bface_ghost)
+    return fail(c, JB_ERR_STATE, "SampleDDMCBlockFace indexed a face probability outside the block (not a 2:1 mesh?)");
+  if (c->h_stats->n_validate)
+    return fail(c, JB_ERR_STATE, "JB_IMC_VALIDATE: " + std::to_string(c->h_stats->n_validate) +
+                                     " index / division cross-checks disagreed");
   if (c->h_stats->n_overflow)
     return fail(c, JB_ERR_CAPACITY, "exchange outbox overflow: raise jb_set_capacity");
   return JB_OK;
@@ -1238,6 +1251,19 @@ jb_status jb_get_particles(jb_ctx *c, const jb_particles *d, int64_t capacity, i
       d->rng[4 * m + 3] = b[m].y;
     }
   }
+  return JB_OK;
+}
+
+jb_status jb_set_sort_interval(jb_ctx *c, int32_t every_n_cycles) {
+  if (!c || every_n_cycles < 0) return JB_ERR_INVALID;
+  c->cfg.sort_interval = every_n_cycles;
+  c->cycles_since_sort = 0;
+  return JB_OK;
+}
+
+jb_status jb_reset_streams(jb_ctx *c) {
+  if (!c) return JB_ERR_INVALID;
+  c->source_call = 0;
   return JB_OK;
 }
 

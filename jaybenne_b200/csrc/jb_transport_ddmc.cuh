@@ -293,7 +293,8 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
         double xi_abs, xi_sc;
         rng.draw2(k0, k1, xi_abs, xi_sc);
         int di, dj, dk;
-        imc_step_lockstep<NDIM>(xi_abs, xi_sc, t_end, c, vv, B.dx_push, p, is_absorbed, is_scattered, di, dj, dk);
+        unsigned bad_div = 0;
+        imc_step_lockstep<NDIM>(xi_abs, xi_sc, t_end, c, vv, B.dx_push, p, is_absorbed, is_scattered, di, dj, dk, bad_div);
         p.ip += di; p.jp += dj; p.kp += dk;  // the face nudges move the index exactly (see k_transport_imc)
       }
       int kind = (is_ddmc_step ? JB_EV_DDMC : 0) | (is_rejected ? JB_EV_ALBEDO_REJECT : 0);

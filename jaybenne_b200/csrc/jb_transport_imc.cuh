@@ -87,40 +87,53 @@ struct Rng2 {
 // ptcl_transport_step (transport_utils.hpp:111-160) with the two draws handed in and the
 // face-distance branches written as selects. Operation for operation the arithmetic of
 // imc_step_idx (jb_device.cuh): a direction with v == 0 computes an unused quotient.
-template <int NDIM>
+// div_normal with the VALIDATE cross-check: the IEEE `/` is evaluated beside it and a differing bit pattern
+// counted (`used` is false where the reference never looks at the quotient, e.g. a direction with v == 0)
+template <bool CHECK>
+__device__ __forceinline__ double divn(const double a, const double b, unsigned &bad, const bool used = true) {
+  const double q = jbm::div_normal(a, b);
+  if (CHECK) {
+    const double r = a / b;
+    if (used && __double_as_longlong(q) != __double_as_longlong(r)) bad++;
+  }
+  return q;
+}
+
+template <int NDIM, bool CHECK = false>
 __device__ __forceinline__ void imc_step_lockstep(const double xi_abs, const double xi_sc, const double t_end,
                                                   const CellEnv &c, const double vv, const double dx_cell, Photon &p,
-                                                  bool &is_absorbed, bool &is_scattered, int &di, int &dj, int &dk) {
+                                                  bool &is_absorbed, bool &is_scattered, int &di, int &dj, int &dk,
+                                                  unsigned &bad) {
   constexpr bool multi_d = NDIM >= 2, three_d = NDIM == 3;
   const double rmin = DBL_MIN;
   // denominators are >= rmin = DBL_MIN (a normal number) and far below overflow: no range test needed
-  const double lam_abs = jbm::div_normal(1.0, c.ff * c.aa + rmin);
-  const double lam_sc = jbm::div_normal(1.0, c.ss + (1.0 - c.ff) * c.aa + rmin);
+  const double lam_abs = divn<CHECK>(1.0, c.ff * c.aa + rmin, bad);
+  const double lam_sc = divn<CHECK>(1.0, c.ss + (1.0 - c.ff) * c.aa + rmin, bad);
   const double dx_abs = -lam_abs * jbm::log_unit(xi_abs);
   const double dx_sc = -lam_sc * jbm::log_unit(xi_sc);
   const double dx_end = vv * (t_end - p.t);
   double dx_push = jbm::min2(dx_cell, dx_end);
   {
     const double face = p.vx > 0.0 ? c.xu : c.xl;
-    const double d = jbm::div_normal(vv * (face - p.x), p.vx);  // |v| is 0 (result unused) or >= ~1e-7
+    const double d = divn<CHECK>(vv * (face - p.x), p.vx, bad, p.vx != 0.0);  // |v| is 0 (result unused) or >= ~1e-7
     const double dm = jbm::min2(dx_push, d);
     dx_push = (p.vx != 0.0) ? dm : dx_push;
   }
   if (multi_d) {
     const double face = p.vy > 0.0 ? c.yu : c.yl;
-    const double d = jbm::div_normal(vv * (face - p.y), p.vy);
+    const double d = divn<CHECK>(vv * (face - p.y), p.vy, bad, p.vy != 0.0);
     const double dm = jbm::min2(dx_push, d);
     dx_push = (p.vy != 0.0) ? dm : dx_push;
   }
   if (three_d) {
     const double face = p.vz > 0.0 ? c.zu : c.zl;
-    const double d = jbm::div_normal(vv * (face - p.z), p.vz);
+    const double d = divn<CHECK>(vv * (face - p.z), p.vz, bad, p.vz != 0.0);
     const double dm = jbm::min2(dx_push, d);
     dx_push = (p.vz != 0.0) ? dm : dx_push;
   }
   is_absorbed = ((dx_abs < dx_push) && (dx_abs < dx_sc));
   is_scattered = (!is_absorbed && (dx_sc < dx_push));
-  const double dt_push = jbm::div_normal(is_absorbed ? dx_abs : (is_scattered ? dx_sc : dx_push), vv);  // <= dx_cell
+  const double dt_push = divn<CHECK>(is_absorbed ? dx_abs : (is_scattered ? dx_sc : dx_push), vv, bad);  // <= dx_cell
   p.t += dt_push;
   p.x += p.vx * dt_push;
   p.y += (multi_d ? 1.0 : 0.0) * p.vy * dt_push;
@@ -292,7 +305,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
               load_block(m, gid, B);
               int ti, tj, tk;
               xtoijk<NDIM>(B, p, ti, tj, tk);
-              if (ti != p.ip || tj != p.jp || tk != p.kp) atomicAdd(&P.stats->n_error, 1ull);
+              if (ti != p.ip || tj != p.jp || tk != p.kp) atomicAdd(&P.stats->n_validate, 1ull);
             }
             have = true;
           }
@@ -362,13 +375,16 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
       }
       bool is_absorbed = false, is_scattered = false;
       int di, dj, dk;
-      imc_step_lockstep<NDIM>(xi_abs, xi_sc, t_end, c, vv, dx_cell, p, is_absorbed, is_scattered, di, dj, dk);
+      unsigned bad_div = 0;
+      imc_step_lockstep<NDIM, VALIDATE>(xi_abs, xi_sc, t_end, c, vv, dx_cell, p, is_absorbed, is_scattered, di, dj, dk,
+                                        bad_div);
+      if (VALIDATE && bad_div) atomicAdd(&P.stats->n_validate, (unsigned long long)bad_div);
       if (VALIDATE) {
         BlkReg B;
         load_block(m, gid, B);
         int ti, tj, tk;
         xtoijk<NDIM>(B, p, ti, tj, tk);
-        if (ti != p.ip + di || tj != p.jp + dj || tk != p.kp + dk) atomicAdd(&P.stats->n_error, 1ull);
+        if (ti != p.ip + di || tj != p.jp + dj || tk != p.kp + dk) atomicAdd(&P.stats->n_validate, 1ull);
       }
       p.ip += di; p.jp += dj; p.kp += dk;
       bool gone = false;
@@ -402,7 +418,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
               xtoijk<NDIM>(B, p, ti, tj, tk);
               bad = ti != p.ip || tj != p.jp || tk != p.kp;
             }
-            if (bad) atomicAdd(&P.stats->n_error, 1ull);
+            if (bad) atomicAdd(&P.stats->n_validate, 1ull);
           }
           if (ngid < 0) {
             atomicAdd(&P.stats->n_error, 1ull);
@@ -478,7 +494,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
   warp_add_energy(P, EB_ABSORBED, e_abs);
 }
 
-static TransportTuning g_tuning = {1, 8, 4, 0};
+static TransportTuning g_tuning = {2, 8, 4, 0};
 void set_transport_tuning(const TransportTuning &t) { g_tuning = t; }
 
 template <int NDIM, int MINB, bool VALIDATE>

@@ -103,9 +103,32 @@ CI_OVERRIDES["stepdiff_smr_ddmc"] = CI_OVERRIDES["stepdiff_smr"]
 CI_OVERRIDES["stepdiff_smr_hybrid"] = CI_OVERRIDES["stepdiff_smr"]
 
 
+
+def _smr3d(jb_extra, dt, sigma, particles):
+    """32^3 root grid in 8^3-cell meshblocks with the central [-0.25, 0.25]^3 refined once: 56 coarse + 64 fine
+    blocks, every face / edge / corner of the fine region a level change in three dimensions."""
+    d = _stepdiff((32, 32, 32), ("-0.5",) * 3, ("0.5",) * 3, (8, 8, 8), jb_extra, refine=_smr_box("0.25"))
+    d["jaybenne"].update({"num_particles": particles, "dt": dt})
+    d["parthenon/time"]["tlim"] = dt
+    d["mcblock"]["scattering_constant_value"] = sigma
+    return d
+
+
+# NOT reference inputs: the reference ships no three-dimensional refined deck, but its 3D code paths
+# (SampleDDMCBlockFace::3D / SampleFace3D, sample_ddmc_bface.cpp:41-78,241-423, and level-changing
+# neighbour look-ups in three dimensions, transport.cpp:146-155) are on the hot path. Same physics as
+# stepdiff_smr*, on a 3D static-refined mesh: pure IMC, every cell DDMC, and a true hybrid
+# (coarse cells tau = 31 > tau_ddmc = 20 > 15.6 = tau of the fine cells).
+EXTRA_DECKS = {
+    "smr3d_imc": _smr3d(None, "3.335641e-12", "1.0e2", 8000),
+    "smr3d_ddmc": _smr3d({"use_ddmc": "true", "tau_ddmc": "2.5"}, "3.335641e-11", "1.0e3", 40000),
+    "smr3d_hybrid": _smr3d({"use_ddmc": "true", "tau_ddmc": "20.0"}, "1.0e-11", "1.0e3", 40000),
+}
+
+
 def deck_text(name: str) -> str:
     lines = []
-    for block, kv in DECKS[name].items():
+    for block, kv in (DECKS[name] if name in DECKS else EXTRA_DECKS[name]).items():
         lines.append(f"<{block}>")
         lines += [f"{k} = {v}" for k, v in kv.items()]
         lines.append("")

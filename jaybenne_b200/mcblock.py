@@ -27,7 +27,7 @@ class ParameterInput:
     """Parthenon-style input deck (blocks of key = value) backed by the C++ reader."""
 
     def __init__(self, path=None, text=None, api=None):
-        self.api = api or capi.device_api()
+        self.api = api or capi.host_api()
         self._deck = capi.deck_p()
         if path is not None:
             st = self.api.deck_load(str(path).encode(), C.byref(self._deck))

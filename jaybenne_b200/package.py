@@ -38,7 +38,7 @@ def default_config(api=None) -> jb_config:
     """jb_config with the reference defaults of the <jaybenne> block (jaybenne.cpp:163-223)."""
     cfg = jb_config()
     if api is None:
-        api = capi.device_api()
+        api = capi.host_api()
     api.config_default(C.byref(cfg))
     return cfg
 
@@ -263,6 +263,13 @@ class Jaybenne:
 
     def clear_particles(self):
         self._check(self.api.set_particles(self._ctx, None, 0))
+
+    def set_sort_interval(self, every_n_cycles: int):
+        self._check(self.api.set_sort_interval(self._ctx, int(every_n_cycles)))
+
+    def reset_streams(self):
+        """Restart the sourcing-call counter of the per-photon streams: the next run repeats the last one."""
+        self._check(self.api.reset_streams(self._ctx))
 
     def comm_init(self, unique_id: bytes):
         self._check(self.api.comm_init(self._ctx, unique_id, self.rank, self.n_ranks))

@@ -1002,7 +1002,12 @@ static jb_status source_photons(Ctx *c, const std::vector<int> &which, int sourc
       static_cast<double>(c->cfg.num_particles) / num_cells / (nblocks_npc * c->mesh.nblocks);
   const uint32_t call = c->source_call;
   std::vector<std::vector<int>> prefix(which.size(), std::vector<int>(num_cells, 0));
-  // pass 1 (SourcePhotons1)
+  const bool serial = c->cfg.rng_mode == JB_RNG_XORSHIFT_POOL;
+  (void)serial;
+  // pass 1 (SourcePhotons1); timing builds take the blocks in parallel (every cell has its own stream)
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(dynamic, 1) if (!serial)
+#endif
   for (size_t w = 0; w < which.size(); ++w) {
     Block &b = c->blocks[which[w]];
     const double dv = b.dx[0] * b.dx[1] * b.dx[2];
@@ -1032,23 +1037,33 @@ static jb_status source_photons(Ctx *c, const std::vector<int> &which, int sourc
     }
   }
   // pass 2 (SourcePhotons2). The new photons of cell ci occupy pool slots base + prefix[ci]..,
-  // i.e. the order a serial push_back would give, so timing builds can run cells in parallel.
+  // i.e. the order a serial push_back would give, so timing builds can run the cells of all blocks in
+  // one parallel region (no barrier between blocks); sums are kept per block and added in block order.
+  std::vector<size_t> bases(which.size(), 0);
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(dynamic, 1) if (!serial)
+#endif
   for (size_t w = 0; w < which.size(); ++w) {
     Block &b = c->blocks[which[w]];
-    const size_t base = b.pool.size();
-    {
-      const int last = num_cells - 1;
-      const size_t nnew = (size_t)prefix[w][last] + (size_t)static_cast<int>(std::round(b.src_num[last]));
-      Particle blank;
-      memset(&blank, 0, sizeof(blank));
-      b.pool.resize(base + nnew, blank);
-    }
+    bases[w] = b.pool.size();
+    const int last = num_cells - 1;
+    const size_t nnew = (size_t)prefix[w][last] + (size_t)static_cast<int>(std::round(b.src_num[last]));
+    Particle blank;
+    memset(&blank, 0, sizeof(blank));
+    b.pool.resize(bases[w] + nnew, blank);
+  }
+  std::vector<long long> sum_n(which.size(), 0);
+  std::vector<double> sum_e(which.size(), 0.0);
+#if defined(_OPENMP)
+#pragma omp parallel if (!serial)
+#endif
+  for (size_t w = 0; w < which.size(); ++w) {
+    Block &b = c->blocks[which[w]];
+    const size_t base = bases[w];
     long long r_n = 0;
     double r_e = 0.0;
-    const bool serial = c->cfg.rng_mode == JB_RNG_XORSHIFT_POOL;
-    (void)serial;
 #if defined(_OPENMP)
-#pragma omp parallel for collapse(3) schedule(static) reduction(+ : r_n, r_e) if (!serial)
+#pragma omp for collapse(3) schedule(static) nowait
 #endif
     for (int k = 0; k < nx3; ++k)
       for (int j = 0; j < nx2; ++j)
@@ -1095,8 +1110,17 @@ static jb_status source_photons(Ctx *c, const std::vector<int> &which, int sourc
             r_e += p.w;
           }
         }
-    c->stats.n_sourced += r_n;
-    c->stats.e_sourced += r_e;
+#if defined(_OPENMP)
+#pragma omp critical(jbo_source_sums)
+#endif
+    {
+      sum_n[w] += r_n;
+      sum_e[w] += r_e;
+    }
+  }
+  for (size_t w = 0; w < which.size(); ++w) {
+    c->stats.n_sourced += sum_n[w];
+    c->stats.e_sourced += sum_e[w];
   }
   c->source_call++;
   return JB_OK;
@@ -1116,19 +1140,28 @@ static jb_status transport_photons(Ctx *c, double t_start, double dt) {
   const bool use_ddmc = c->cfg.use_ddmc != 0;
   const double tau_ddmc = c->cfg.tau_ddmc;
   const int nx1 = c->mesh.nxb[0], nx2 = c->mesh.nxb[1];
-  for (Block &b : c->blocks) {
+  // Timing builds (-fopenmp) spread the photons of ALL blocks over the host threads in one parallel region
+  // without a barrier between blocks — the flat (block, particle) par_for of the reference's MeshData pack
+  // on the Kokkos OpenMP backend (transport.cpp:64-68). Counters are summed per block (thread partial sums
+  // added under a critical section), so a build without OpenMP — the parity builds — runs the very loop
+  // and the very summation order it always had; the tally becomes an atomic add.
+  const size_t nblk = c->blocks.size();
+  struct BlkSums { long long seg = 0, ddmc = 0, abs = 0, scat = 0; double eabs = 0.0; };
+  std::vector<BlkSums> sums(nblk);
+  const bool serial = c->log_events || c->cfg.rng_mode == JB_RNG_XORSHIFT_POOL;
+  (void)serial;
+#if defined(_OPENMP)
+#pragma omp parallel if (!serial)
+#endif
+  for (size_t bi = 0; bi < nblk; ++bi) {
+    Block &b = c->blocks[bi];
     const double dx_i = b.dx[0], dx_j = b.dx[1], dx_k = b.dx[2];
     const double dx_push = std::min(dx_i, std::min(dx_j, dx_k));
-    // Timing builds (-fopenmp) spread the photons of a block over the host threads, like the
-    // reference's Kokkos OpenMP backend does; counters become reductions and the tally an
-    // atomic add. Parity builds are compiled without OpenMP and run this loop serially.
     long long r_seg = 0, r_ddmc = 0, r_abs = 0, r_scat = 0;
     double r_eabs = 0.0;
     const long long npool = (long long)b.pool.size();
-    const bool serial = c->log_events || c->cfg.rng_mode == JB_RNG_XORSHIFT_POOL;
-    (void)serial;
 #if defined(_OPENMP)
-#pragma omp parallel for schedule(dynamic, 1024) reduction(+ : r_seg, r_ddmc, r_abs, r_scat, r_eabs) if (!serial)
+#pragma omp for schedule(dynamic, 1024) nowait
 #endif
     for (long long pi = 0; pi < npool; ++pi) {
       Particle &p = b.pool[pi];
@@ -1216,13 +1249,25 @@ static jb_status transport_photons(Ctx *c, double t_start, double dt) {
       }
       p.rn = rng.n;
     }
-    c->stats.n_segments += r_seg;
-    c->stats.n_ddmc_segments += r_ddmc;
-    c->stats.n_absorbed += r_abs;
-    c->stats.n_scatters += r_scat;
-    c->stats.e_absorbed += r_eabs;
-    remove_marked(b);
+#if defined(_OPENMP)
+#pragma omp critical(jbo_transport_sums)
+#endif
+    {
+      sums[bi].seg += r_seg; sums[bi].ddmc += r_ddmc; sums[bi].abs += r_abs; sums[bi].scat += r_scat;
+      sums[bi].eabs += r_eabs;
+    }
   }
+  for (size_t bi = 0; bi < nblk; ++bi) {
+    c->stats.n_segments += sums[bi].seg;
+    c->stats.n_ddmc_segments += sums[bi].ddmc;
+    c->stats.n_absorbed += sums[bi].abs;
+    c->stats.n_scatters += sums[bi].scat;
+    c->stats.e_absorbed += sums[bi].eabs;
+  }
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(dynamic, 1) if (!serial)
+#endif
+  for (size_t bi = 0; bi < nblk; ++bi) remove_marked(c->blocks[bi]);
   return JB_OK;
 }
 
@@ -1230,24 +1275,46 @@ static jb_status transport_photons(Ctx *c, double t_start, double dt) {
 // that sits off its block gets the swarm boundary conditions applied and is handed to
 // the block that now contains it (same rank: appended to that pool; other rank: outbox).
 static jb_status swarm_exchange_local(Ctx *c) {
-  std::vector<std::pair<int, Particle>> moved;
-  for (Block &b : c->blocks) {
+  // the scan of every pool for off-block particles runs over the blocks in parallel (timing builds); the
+  // leavers are then delivered in block order, which is the order the serial loop always produced
+  const size_t nblk = c->blocks.size();
+  std::vector<std::vector<std::pair<int, Particle>>> moved_by(nblk);
+  std::vector<long long> esc_n(nblk, 0), cross_n(nblk, 0), lost(nblk, 0);
+  std::vector<double> esc_e(nblk, 0.0);
+  const bool serial = c->cfg.rng_mode == JB_RNG_XORSHIFT_POOL;
+  (void)serial;
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(dynamic, 1) if (!serial)
+#endif
+  for (size_t bi = 0; bi < nblk; ++bi) {
+    Block &b = c->blocks[bi];
     for (Particle &p : b.pool) {
       if (on_block(c, p.i, p.j, p.k)) continue;
       Particle q = p;
       p.marked = true;
       if (!apply_swarm_bc(c, q)) {
-        c->stats.n_escaped++;
-        c->stats.e_escaped += q.w;
+        esc_n[bi]++;
+        esc_e[bi] += q.w;
         continue;
       }
       const double pos[3] = {q.x, q.y, q.z};
       const int gid = find_block(c, pos);
-      if (gid < 0) return fail(c, JB_ERR_STATE, "particle left the domain without a boundary condition");
-      c->stats.n_block_crossings++;
-      moved.push_back({gid, q});
+      if (gid < 0) {
+        lost[bi]++;
+        continue;
+      }
+      cross_n[bi]++;
+      moved_by[bi].push_back({gid, q});
     }
     remove_marked(b);
+  }
+  std::vector<std::pair<int, Particle>> moved;
+  for (size_t bi = 0; bi < nblk; ++bi) {
+    if (lost[bi]) return fail(c, JB_ERR_STATE, "particle left the domain without a boundary condition");
+    c->stats.n_escaped += esc_n[bi];
+    c->stats.e_escaped += esc_e[bi];
+    c->stats.n_block_crossings += cross_n[bi];
+    moved.insert(moved.end(), moved_by[bi].begin(), moved_by[bi].end());
   }
   for (auto &m : moved) {
     const int gid = m.first;
@@ -1305,24 +1372,30 @@ static void sample_face_3d(const int i1_l, const int i2_l, const double dx1, con
   }
 }
 
-// SampleDDMCBlockFace, sample_ddmc_bface.cpp:81-427. Face-probability reads at indices
-// one outside the block (the reference reads exchanged ghost faces there) are clamped.
+// SampleDDMCBlockFace, sample_ddmc_bface.cpp:81-427. The reference reads the face probabilities through
+// ghost-inclusive indices; on a 2:1 mesh the two fine cells under a coarse cell never straddle a block
+// edge, so a read one index outside the block cannot happen: it is counted and fails the task (the
+// reference would read an exchanged ghost face there) instead of being clamped silently.
 static jb_status sample_ddmc_block_face(Ctx *c) {
   if (!(c->mesh.ndim > 1)) return JB_OK;
   const double vv = c->cl.c_code;
   const bool three_d = c->mesh.ndim > 2;
   constexpr double eps = EPS10;
   const int n1 = c->mesh.nxb[0], n2 = c->mesh.nxb[1], n3 = c->mesh.nxb[2];
-  auto clampi = [](int v, int lo, int hi) { return std::min(std::max(v, lo), hi); };
+  long long ghost_reads = 0;
+  auto inblock = [&](int v, int lo, int hi) {
+    if (v < lo || v > hi) ++ghost_reads;
+    return std::min(std::max(v, lo), hi);
+  };
   for (Block &b : c->blocks) {
     auto F1 = [&](int k, int j, int i) {
-      return b.fp[0][((size_t)clampi(k, 0, n3 - 1) * n2 + clampi(j, 0, n2 - 1)) * (n1 + 1) + clampi(i, 0, n1)];
+      return b.fp[0][((size_t)inblock(k, 0, n3 - 1) * n2 + inblock(j, 0, n2 - 1)) * (n1 + 1) + inblock(i, 0, n1)];
     };
     auto F2 = [&](int k, int j, int i) {
-      return b.fp[1][((size_t)clampi(k, 0, n3 - 1) * (n2 + 1) + clampi(j, 0, n2)) * n1 + clampi(i, 0, n1 - 1)];
+      return b.fp[1][((size_t)inblock(k, 0, n3 - 1) * (n2 + 1) + inblock(j, 0, n2)) * n1 + inblock(i, 0, n1 - 1)];
     };
     auto F3 = [&](int k, int j, int i) {
-      return b.fp[2][((size_t)clampi(k, 0, n3) * n2 + clampi(j, 0, n2 - 1)) * n1 + clampi(i, 0, n1 - 1)];
+      return b.fp[2][((size_t)inblock(k, 0, n3) * n2 + inblock(j, 0, n2 - 1)) * n1 + inblock(i, 0, n1 - 1)];
     };
     const double bx0 = b.info.xmin[0], bx1 = b.info.xmax[0];
     const double by0 = b.info.xmin[1], by1 = b.info.xmax[1];
@@ -1354,6 +1427,7 @@ static jb_status sample_ddmc_block_face(Ctx *c) {
           if (at_y_edge_u || at_y_edge_l) {
             const int jp_u = at_y_edge_u ? jp : jp + 1;
             const int jp_l = at_y_edge_u ? jp - 1 : jp;
+            ++c->stats.n_bface_resampled;
             sample_face_2d(jp_l, dy_j, F1(kp, jp_l, ip_b), F1(kp, jp_u, ip_b), rng, jp, y);
           }
         } else {
@@ -1364,6 +1438,7 @@ static jb_status sample_ddmc_block_face(Ctx *c) {
             const int kp_u = at_z_edge_u ? kp : kp + 1, kp_l = at_z_edge_u ? kp - 1 : kp;
             const double Px_uu = F1(kp_u, jp_u, ip_b), Px_ul = F1(kp_u, jp_l, ip_b);
             const double Px_lu = F1(kp_l, jp_u, ip_b), Px_ll = F1(kp_l, jp_l, ip_b);
+            ++c->stats.n_bface_resampled;
             sample_face_3d(jp_l, kp_l, dy_j, dz_k, Px_ll, Px_lu, Px_ul, Px_uu, rng, jp, kp, y, z);
           }
         }
@@ -1377,6 +1452,7 @@ static jb_status sample_ddmc_block_face(Ctx *c) {
           if (at_x_edge_u || at_x_edge_l) {
             const int ip_u = at_x_edge_u ? ip : ip + 1;
             const int ip_l = at_x_edge_u ? ip - 1 : ip;
+            ++c->stats.n_bface_resampled;
             sample_face_2d(ip_l, dx_i, F2(kp, jp_b, ip_l), F2(kp, jp_b, ip_u), rng, ip, x);
           }
         } else {
@@ -1387,6 +1463,7 @@ static jb_status sample_ddmc_block_face(Ctx *c) {
             const int ip_u = at_x_edge_u ? ip : ip + 1, ip_l = at_x_edge_u ? ip - 1 : ip;
             const double Py_uu = F2(kp_u, jp_b, ip_u), Py_ul = F2(kp_u, jp_b, ip_l);
             const double Py_lu = F2(kp_l, jp_b, ip_u), Py_ll = F2(kp_l, jp_b, ip_l);
+            ++c->stats.n_bface_resampled;
             sample_face_3d(ip_l, kp_l, dx_i, dz_k, Py_ll, Py_lu, Py_ul, Py_uu, rng, ip, kp, x, z);
           }
         }
@@ -1403,12 +1480,15 @@ static jb_status sample_ddmc_block_face(Ctx *c) {
           const int jp_u = at_y_edge_u ? jp : jp + 1, jp_l = at_y_edge_u ? jp - 1 : jp;
           const double Pz_uu = F3(kp_b, jp_u, ip_u), Pz_ul = F3(kp_b, jp_u, ip_l);
           const double Pz_lu = F3(kp_b, jp_l, ip_u), Pz_ll = F3(kp_b, jp_l, ip_l);
+          ++c->stats.n_bface_resampled;
           sample_face_3d(ip_l, jp_l, dx_i, dy_j, Pz_ll, Pz_lu, Pz_ul, Pz_uu, rng, ip, jp, x, y);
         }
       }
       p.rn = rng.n;
     }
   }
+  if (ghost_reads)
+    return fail(c, JB_ERR_STATE, "SampleDDMCBlockFace indexed a face probability outside the block (not a 2:1 mesh?)");
   return JB_OK;
 }
 
@@ -1423,7 +1503,11 @@ static int64_t check_completion(Ctx *c, double t_end) {
 
 // EvaluateRadiationEnergy, jaybenne.cpp:514-564
 static void evaluate_radiation_energy(Ctx *c) {
-  for (Block &b : c->blocks) {
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(dynamic, 1)
+#endif
+  for (size_t bi = 0; bi < c->blocks.size(); ++bi) {
+    Block &b = c->blocks[bi];
     std::fill(b.tally.begin(), b.tally.end(), 0.0);
     const double dv = b.dx[0] * b.dx[1] * b.dx[2];
     for (Particle &p : b.pool) b.tally[cidx(c, p.k, p.j, p.i)] += p.w / dv;
@@ -1433,7 +1517,11 @@ static void evaluate_radiation_energy(Ctx *c) {
 // UpdateFluid, jaybenne.cpp:583-615
 static void update_fluid(Ctx *c) {
   if (!c->cfg.do_feedback) return;
-  for (Block &b : c->blocks) {
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(static)
+#endif
+  for (size_t bi = 0; bi < c->blocks.size(); ++bi) {
+    Block &b = c->blocks[bi];
     const double dv = b.dx[0] * b.dx[1] * b.dx[2];
     for (size_t ci = 0; ci < b.u.size(); ++ci) {
       const double delta = b.edelta[ci] / dv;
@@ -1443,6 +1531,29 @@ static void update_fluid(Ctx *c) {
 }
 
 static void census_sums(Ctx *c, int64_t &n, double &e) {
+#if defined(_OPENMP)
+  // timing builds: per-block partial sums in parallel, added in block order
+  const size_t nblk = c->blocks.size();
+  std::vector<int64_t> bn(nblk, 0);
+  std::vector<double> be(nblk, 0.0);
+#pragma omp parallel for schedule(dynamic, 1)
+  for (size_t bi = 0; bi < nblk; ++bi) {
+    int64_t nn = 0;
+    double ee = 0.0;
+    for (Particle &p : c->blocks[bi].pool) {
+      nn++;
+      ee += p.w;
+    }
+    bn[bi] = nn;
+    be[bi] = ee;
+  }
+  n = 0;
+  e = 0.0;
+  for (size_t bi = 0; bi < nblk; ++bi) {
+    n += bn[bi];
+    e += be[bi];
+  }
+#else
   n = 0;
   e = 0.0;
   for (Block &b : c->blocks)
@@ -1450,6 +1561,7 @@ static void census_sums(Ctx *c, int64_t &n, double &e) {
       n++;
       e += p.w;
     }
+#endif
 }
 
 }  // namespace jbo
@@ -1463,6 +1575,22 @@ struct jb_ctx : public jbo::Ctx {};
 extern "C" {
 
 const char *jbo_flavour(void) { return JBO_FLAVOUR; }
+
+// host threads of the timing builds (bench.py's CPU arm sets and reports them; parity builds have one)
+int32_t jbo_max_threads(void) {
+#if defined(_OPENMP)
+  return (int32_t)omp_get_max_threads();
+#else
+  return 1;
+#endif
+}
+void jbo_set_num_threads(int32_t n) {
+#if defined(_OPENMP)
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
 
 void jbo_config_default(jb_config *cfg) {
   memset(cfg, 0, sizeof(*cfg));
@@ -1752,6 +1880,10 @@ jb_status jbo_get_particles(jb_ctx *c, const jb_particles *d, int64_t capacity, 
   return JB_OK;
 }
 
+jb_status jbo_reset_streams(jb_ctx *c) {
+  c->source_call = 0;
+  return JB_OK;
+}
 jb_status jbo_set_particles(jb_ctx *c, const jb_particles *s, int64_t n) {
   for (auto &b : c->blocks) b.pool.clear();
   for (int64_t m = 0; m < n; ++m) {

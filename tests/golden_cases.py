@@ -169,9 +169,14 @@ RUNS = {
     "stepdiff_smr_ci": ("stepdiff_smr", True, [("jaybenne", "num_particles", 3000)], 2),
     "stepdiff_smr_ddmc_ci": ("stepdiff_smr_ddmc", True, [("jaybenne", "num_particles", 6000)], 2),
     "stepdiff_smr_hybrid_shipped": ("stepdiff_smr_hybrid", False, [("jaybenne", "num_particles", 6000)], 1),
+    # three-dimensional static refinement (jaybenne_b200/decks.py EXTRA_DECKS): level-changing crossings in 3D,
+    # SampleDDMCBlockFace::3D / SampleFace3D (n_bface_resampled > 0)
+    "smr3d_imc": ("smr3d_imc", False, [], 2),
+    "smr3d_ddmc": ("smr3d_ddmc", False, [], 2),
+    "smr3d_hybrid": ("smr3d_hybrid", False, [("jaybenne", "num_particles", 12000), ("jaybenne", "dt", "5.0e-12")], 2),
 }
 COUNT_KEYS = ("n_start", "n_sourced", "n_absorbed", "n_escaped", "n_end", "n_segments", "n_scatters",
-              "n_ddmc_segments", "n_block_crossings")
+              "n_ddmc_segments", "n_block_crossings", "n_bface_resampled")
 ENERGY_KEYS = ("e_start", "e_sourced", "e_absorbed", "e_escaped", "e_end")
 
 

@@ -19,6 +19,8 @@ _cache = {}
 
 PROBES = {
     "flavour": (C.c_char_p, []),
+    "max_threads": (C.c_int32, []),
+    "set_num_threads": (None, [C.c_int32]),
     "config_default": (None, [C.POINTER(capi.jb_config)]),
     "probe_absorption": (C.c_double, [capi.ctx_p, C.c_double, C.c_double, C.c_double]),
     "probe_scattering": (C.c_double, [capi.ctx_p, C.c_double, C.c_double, C.c_double]),

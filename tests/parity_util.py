@@ -11,7 +11,7 @@ from jaybenne_b200.decks import CI_OVERRIDES, deck_text
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 COUNT_KEYS = ("n_start", "n_sourced", "n_absorbed", "n_escaped", "n_end", "n_segments", "n_scatters",
-              "n_ddmc_segments", "n_block_crossings")
+              "n_ddmc_segments", "n_block_crossings", "n_bface_resampled")
 ENERGY_KEYS = ("e_start", "e_sourced", "e_absorbed", "e_escaped", "e_end")
 
 

@@ -33,6 +33,22 @@ def test_reference_arm_prints_the_contract_line():
     assert d["gpu_launches"] == 0 and "workload" in d["config"]
 
 
+def test_reference_arm_labels_are_true_under_torchrun_environment():
+    """`torch.distributed.run` with nproc > 1 exports OMP_NUM_THREADS=1: the arm must set its thread count itself,
+    report what OpenMP then says, name the twin it actually ran in `config`, and not map the CUDA library."""
+    r = run_bench(["--impl", "reference", "--gpus", "2", "--cells", "32", "--cpu-cells", "16", "--steps", "1", "--warmup", "1"],
+                  env={"RANK": "0", "WORLD_SIZE": "2", "LOCAL_RANK": "0", "OMP_NUM_THREADS": "1"})
+    assert r.returncode == 0, r.stderr
+    d = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][0])
+    want = len(os.sched_getaffinity(0))
+    assert d["cpu_baseline"]["cores"] == want, (d["cpu_baseline"]["cores"], want)
+    cfg = d["config"]
+    assert cfg["cells"] == 16 and cfg["twin_of"]["cells"] == 32 and abs(cfg["photons_per_step"] - cfg["twin_of"]["photons_per_step"] / 8) <= 1
+    assert cfg["shrunk_to_fit_time_budget"] is False and cfg["omp_num_threads_env"] == "1"
+    assert "16^3 cells" in cfg["workload"] and cfg["cuda_library_mapped"] is False
+    assert f"{want} threads" in d["cpu_baseline"]["sample"]
+
+
 def test_reference_arm_other_ranks_exit_quietly():
     r = run_bench(["--impl", "reference", "--gpus", "2", "--cells", "16"], env={"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"})
     assert r.returncode == 0 and r.stdout.strip() == ""

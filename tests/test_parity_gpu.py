@@ -367,3 +367,117 @@ def test_hybrid_deck_event_by_event():
         assert np.array_equal(eg[f], eo[f]), f
     for f in ("t", "x", "y", "z", "v0", "v1", "v2"):
         assert np.array_equal(eg[f], eo[f]), f
+
+
+# ---- kernel variants and the VALIDATE cross-checks -------------------------------------------------
+VARIANT_DECKS = {
+    "synthetic3d": dict(text=pu.synthetic_text(n=16, nb=8, num_particles=30000), density=True, cycles=3),
+    "synthetic2d": dict(text=pu.synthetic_text(n=16, nb=8, num_particles=6000, ndim=2), density=True, cycles=2),
+    "stepdiff_reflecting": dict(deck="stepdiff", overrides=[("jaybenne", "num_particles", 3000)], cycles=2),
+    "stepdiff_smr_levels": dict(deck="stepdiff_smr", ci=True, overrides=[("jaybenne", "num_particles", 4000)], cycles=2),
+    "outflow": dict(text=pu.synthetic_text(n=8, nb=4, num_particles=4000, kappa=0.0, sigma=1.0).replace("periodic", "outflow"),
+                    cycles=1),
+}
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2])
+@pytest.mark.parametrize("name", sorted(VARIANT_DECKS))
+def test_imc_kernel_variants_are_bit_identical_to_the_oracle(monkeypatch, variant, name):
+    """JB_TRANSPORT_VARIANT: 0 = thread per photon, 1 = persistent warps with lane refill (v9), 2 = warp-private
+    photon pools in shared memory (v10, the default). Streams are per photon, so every variant must give the
+    oracle's swarm bit for bit."""
+    monkeypatch.setenv("JB_TRANSPORT_VARIANT", str(variant))
+    d = VARIANT_DECKS[name]
+    gpu, ora = pu.make_pair(d.get("deck"), text=d.get("text"), overrides=d.get("overrides", ()), ci=d.get("ci", False))
+    sg, _ = run_pair(gpu, ora, cycles=d["cycles"], density_fn=pu.synthetic_density if d.get("density") else None)
+    assert sg["n_segments"] > 0
+
+
+@pytest.mark.parametrize("slots,refill,low", [(56, 1, 1), (56, 32, 32), (64, 16, 24), (64, 8, 32)])
+def test_pool_kernel_tuning_does_not_change_results(monkeypatch, slots, refill, low):
+    """The pool kernel's phase thresholds only change the order in which a warp visits its photons."""
+    monkeypatch.setenv("JB_TRANSPORT_VARIANT", "2")
+    monkeypatch.setenv("JB_POOL_SLOTS", str(slots))
+    monkeypatch.setenv("JB_POOL_REFILL_MIN", str(refill))
+    monkeypatch.setenv("JB_POOL_READY_LOW", str(low))
+    gpu, ora = pu.make_pair(text=pu.synthetic_text(n=16, nb=8, num_particles=30000))
+    run_pair(gpu, ora, cycles=3, density_fn=pu.synthetic_density)
+
+
+@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("name", sorted(VARIANT_DECKS))
+def test_validate_build_finds_no_disagreement(monkeypatch, variant, name):
+    """JB_IMC_VALIDATE=1 runs the instantiation that re-derives every cell index / block with Xtoijk / find_block
+    beside the index-increment shortcut and evaluates the IEEE `/` beside every div_normal; a disagreement makes
+    the step fail (DStats::n_validate)."""
+    monkeypatch.setenv("JB_TRANSPORT_VARIANT", str(variant))
+    monkeypatch.setenv("JB_IMC_VALIDATE", "1")
+    d = VARIANT_DECKS[name]
+    gpu, ora = pu.make_pair(d.get("deck"), text=d.get("text"), overrides=d.get("overrides", ()), ci=d.get("ci", False))
+    run_pair(gpu, ora, cycles=d["cycles"], density_fn=pu.synthetic_density if d.get("density") else None)
+
+
+def test_validate_build_at_128_cubed(monkeypatch):
+    """The same cross-checks at 128^3 cells / 1.25e8 photons (1e9 segments, 6e9 divisions): the step must not
+    report a single disagreement, and must give the counts of the production instantiation."""
+    from jaybenne_b200 import Mcblock, device_api
+    text = pu.synthetic_text(n=128, nb=32, num_particles=int(1.25e8))
+    out = []
+    for validate in ("1", "0"):
+        monkeypatch.setenv("JB_IMC_VALIDATE", validate)
+        mb = Mcblock(pu.make_pin(text=text), api=device_api(), capacity=int(1.3e8), cfg_overrides={"source_nblocks": 64})
+        mb.ProblemGenerator(pu.synthetic_density)
+        st = mb.Step()           # raises on n_validate != 0
+        out.append({k: st[k] for k in pu.COUNT_KEYS})
+        del mb
+    assert out[0] == out[1], out
+    assert out[0]["n_segments"] > 9e8
+
+
+# ---- three-dimensional static refinement (decks.EXTRA_DECKS; goldens: runs.json smr3d_*) ---------------
+def test_smr3d_imc_level_changes_in_three_dimensions():
+    """Pure IMC on 56 coarse + 64 fine blocks: photons cross faces, edges and corners between levels in 3D
+    (find_block + Xtoijk on the finer / coarser side, transport.cpp:146-155)."""
+    gpu, ora = pu.make_pair("smr3d_imc")
+    assert gpu.mesh.c.max_level == 1 and gpu.mesh.nblocks == 120 and gpu.mesh.c.ndim == 3
+    sg, _ = run_pair(gpu, ora, cycles=2)
+    assert sg["n_block_crossings"] > 1000
+
+
+def test_smr3d_ddmc_block_face_resampling_in_three_dimensions():
+    """Every cell DDMC (tau_ddmc = 2.5): leaks out of coarse blocks into fine ones arrive on a fine-cell VERTEX
+    and go through SampleDDMCBlockFace::3D / SampleFace3D (sample_ddmc_bface.cpp:41-78,241-423)."""
+    gpu, ora = pu.make_pair("smr3d_ddmc")
+    sg, so = run_pair(gpu, ora, cycles=2, fields=False)
+    assert sg["n_ddmc_segments"] == sg["n_segments"] > 0
+    assert sg["n_bface_resampled"] == so["n_bface_resampled"] > 100      # SampleFace3D draws happened
+    for gid in gpu.jb.local_gids[::7]:
+        for d in ("x1", "x2", "x3"):
+            a, b = gpu.jb.get_field(gid, "ddmc_face_prob_" + d), ora.jb.get_field(gid, "ddmc_face_prob_" + d)
+            assert np.array_equal(a, b), (gid, d)
+
+
+def test_smr3d_hybrid_true_hybrid_in_three_dimensions():
+    """tau_ddmc = 20 between the optical depths of the fine (15.6) and the coarse (31) cells: IMC inside the
+    refined region, DDMC outside, albedo + block-face resampling at the 3D level boundary."""
+    gpu, ora = pu.make_pair("smr3d_hybrid", overrides=[("jaybenne", "num_particles", 12000), ("jaybenne", "dt", "5.0e-12")])
+    sg, _ = run_pair(gpu, ora, cycles=2, fields=False)
+    assert 0 < sg["n_ddmc_segments"] < sg["n_segments"] and sg["n_bface_resampled"] > 0
+
+
+def test_smr3d_hybrid_event_by_event():
+    gpu, ora = pu.make_pair("smr3d_hybrid", overrides=[("jaybenne", "num_particles", 12000), ("jaybenne", "dt", "1.0e-12")])
+    gpu.ProblemGenerator(); ora.ProblemGenerator()
+    cap = 3000000
+    gpu.jb.event_log_enable(cap); ora.jb.event_log_enable(cap)
+    sg, so = gpu.Step(), ora.Step()
+    pu.assert_stats_equal(sg, so)
+    eg, eo = gpu.jb.events(), ora.jb.events()
+    assert len(eg) == len(eo) and 0 < len(eg) < cap
+    assert sg["n_ddmc_segments"] > 0 and sg["n_segments"] > sg["n_ddmc_segments"] and sg["n_block_crossings"] > 0
+    key = lambda e: np.lexsort((e["draw"], e["id_idx"], e["id_gid"], e["id_call"]))
+    eg, eo = eg[key(eg)], eo[key(eo)]
+    for f in ("id_idx", "id_gid", "id_call", "draw", "kind", "block", "i", "j", "k"):
+        assert np.array_equal(eg[f], eo[f]), f
+    for f in ("t", "x", "y", "z", "v0", "v1", "v2"):
+        assert np.array_equal(eg[f], eo[f]), f
