@@ -7,6 +7,7 @@
 // returns JB_ERR_NO_DEVICE.
 #include <dlfcn.h>
 #include <nccl.h>
+#include <nvtx3/nvToolsExt.h>  // header-only NVTX v3: ranges cost nothing unless a tool is attached
 
 #include <algorithm>
 #include <cmath>
@@ -52,6 +53,14 @@ static NcclApi &nccl_api() {
            api.Recv && api.GroupStart && api.GroupEnd;
   return api;
 }
+
+// the reference's Kokkos::Profiling regions (jaybenne.cpp:87,115,127,145) as NVTX ranges with the same names
+struct NvtxRange {
+  explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange &) = delete;
+  NvtxRange &operator=(const NvtxRange &) = delete;
+};
 
 struct jb_ctx {
   jb_config cfg;
@@ -339,7 +348,7 @@ jb_status jb_create(const jb_config *cfg, jb_ctx **out) {
             dalloc(&c->d_esum, 2) == cudaSuccess && dalloc(&c->d_total, 2) == cudaSuccess &&
             dalloc(&c->d_ebins, (long long)EB_KINDS * EBINS) == cudaSuccess &&
             cudaMallocHost((void **)&c->h_stats, sizeof(DStats)) == cudaSuccess &&
-            cudaMallocHost((void **)&c->h_counters, sizeof(unsigned long long) * (16 + 64 * 64)) == cudaSuccess;
+            cudaMallocHost((void **)&c->h_counters, sizeof(unsigned long long) * (16 + 64 * 67)) == cudaSuccess;
   if (!ok) {
     delete c;
     return JB_ERR_CUDA;
@@ -542,7 +551,7 @@ jb_status jb_set_mesh(jb_ctx *c, const jb_mesh *m, int32_t my_rank, int32_t n_ra
   JB_CUDA(c, dalloc(&c->d_cnt, c->ncells_local));
   JB_CUDA(c, dalloc(&c->d_prefix, c->ncells_local + 1));
   JB_CUDA(c, dalloc(&c->d_scan, scan_scratch_elems(std::max<long long>(c->ncells_local, 1))));
-  JB_CUDA(c, dalloc(&c->d_count_matrix, (long long)n_ranks * n_ranks));
+  JB_CUDA(c, dalloc(&c->d_count_matrix, (long long)n_ranks * (n_ranks + 3) + (n_ranks + 3)));
   c->mesh_set = true;
   return JB_OK;
 }
@@ -826,27 +835,58 @@ static jb_status exchange_nccl(jb_ctx *c, double t_end, long long *global_sent) 
     if (r_ != ncclSuccess)                                                                             \
       return fail(c, JB_ERR_COMM, std::string(#call) + ": " + (nc.GetErrorString ? nc.GetErrorString(r_) : "?")); \
   } while (0)
-  JB_NCCL(nc.AllGather(c->out.count, c->d_count_matrix, (size_t)R, ncclUint64, c->comm, c->stream));
-  JB_CUDA(c, cudaMemcpyAsync(c->h_counters + 16, c->d_count_matrix, sizeof(unsigned long long) * R * R,
+  // Every rank gathers every rank's row: the R outbox counts, then its outbox capacity, its inbox capacity and
+  // the room left in its pool (all ones = the pool may grow). With the whole table on every rank, a buffer
+  // that would overflow ANYWHERE fails the call on ALL ranks before any of them enters the send / receive
+  // group — a rank returning alone would leave its peers hanging in ncclGroupEnd.
+  const int RW = R + 3;
+  unsigned long long *d_row = c->d_count_matrix + (size_t)R * RW;
+  {
+    unsigned long long *h_row = c->h_counters + 8;
+    h_row[0] = (unsigned long long)c->out.cap;
+    h_row[1] = (unsigned long long)c->inbox_cap;
+    h_row[2] = c->requested_capacity > 0 ? (unsigned long long)std::max<long long>(c->capacity - c->n, 0) : ~0ull;
+    JB_CUDA(c, cudaMemcpyAsync(d_row, c->out.count, sizeof(unsigned long long) * R, cudaMemcpyDeviceToDevice, c->stream));
+    JB_CUDA(c, cudaMemcpyAsync(d_row + R, h_row, sizeof(unsigned long long) * 3, cudaMemcpyHostToDevice, c->stream));
+  }
+  JB_NCCL(nc.AllGather(d_row, c->d_count_matrix, (size_t)RW, ncclUint64, c->comm, c->stream));
+  JB_CUDA(c, cudaMemcpyAsync(c->h_counters + 16, c->d_count_matrix, sizeof(unsigned long long) * R * RW,
                              cudaMemcpyDeviceToHost, c->stream));
   JB_CUDA(c, cudaStreamSynchronize(c->stream));
-  const unsigned long long *M = c->h_counters + 16;  // M[src * R + dst]
+  const unsigned long long *T = c->h_counters + 16;  // T[src * RW + dst], then src's out.cap, inbox_cap, room
+  auto Mat = [&](int a, int b) { return (long long)T[(size_t)a * RW + b]; };
   long long total = 0, nrecv = 0;
-  for (int a = 0; a < R; ++a)
-    for (int b = 0; b < R; ++b) total += (long long)M[a * R + b];
-  for (int a = 0; a < R; ++a) nrecv += (long long)M[a * R + c->my_rank];
+  std::string problem;
+  for (int a = 0; a < R; ++a) {
+    const unsigned long long out_cap_a = T[(size_t)a * RW + R];
+    long long col = 0;
+    for (int b = 0; b < R; ++b) {
+      total += Mat(a, b);
+      col += Mat(b, a);
+      if ((unsigned long long)Mat(a, b) > out_cap_a && problem.empty())
+        problem = "exchange outbox overflow on rank " + std::to_string(a) + " (records for rank " + std::to_string(b) +
+                  "): raise jb_set_capacity";
+    }
+    if ((unsigned long long)col > T[(size_t)a * RW + R + 1] && problem.empty())
+      problem = "exchange inbox overflow on rank " + std::to_string(a) + ": raise jb_set_capacity";
+    if ((unsigned long long)col > T[(size_t)a * RW + R + 2] && problem.empty())
+      problem = "photon pool capacity exceeded on receive on rank " + std::to_string(a);
+  }
+  for (int a = 0; a < R; ++a) nrecv += Mat(a, c->my_rank);
   *global_sent = total;
+  if (!problem.empty()) {  // the same verdict on every rank: nobody sends
+    cudaMemsetAsync(c->out.count, 0, sizeof(unsigned long long) * R, c->stream);
+    return fail(c, JB_ERR_CAPACITY, problem);
+  }
   if (total == 0) return JB_OK;
-  if (nrecv > c->inbox_cap) return fail(c, JB_ERR_CAPACITY, "exchange inbox overflow: raise jb_set_capacity");
-  if (c->n + nrecv > c->capacity) {
-    if (c->requested_capacity > 0) return fail(c, JB_ERR_CAPACITY, "photon pool capacity exceeded on receive");
+  if (c->n + nrecv > c->capacity) {  // only pools that may grow get here (the fixed ones were checked above)
     jb_status gs = grow_pool_only(c, c->n + nrecv);
     if (gs != JB_OK) return gs;
   }
   JB_NCCL(nc.GroupStart());
   long long roff = 0;
   for (int peer = 0; peer < R; ++peer) {
-    const long long ns = (long long)M[c->my_rank * R + peer], nr = (long long)M[peer * R + c->my_rank];
+    const long long ns = std::min(Mat(c->my_rank, peer), c->out.cap), nr = Mat(peer, c->my_rank);
     if (ns > 0)
       JB_NCCL(nc.Send(c->out.rec + (size_t)peer * c->out.cap, (size_t)ns * sizeof(ExRecord), ncclUint8, peer, c->comm,
                       c->stream));
@@ -1121,6 +1161,7 @@ jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats
   JB_REQUIRE_MESH(c);
   if (c->n_ranks > 1 && !c->comm)
     return fail(c, JB_ERR_COMM, "multi-rank step needs jb_comm_init (or drive the tasks and jb_exchange_* from the host)");
+  NvtxRange timestep_range("Jaybenne::Timestep");
   cudaEventRecord(c->ev[0], c->stream);
   jb_status s = JB_OK;
   // a fixed-size pool that also has to take arrivals from other ranks starts the cycle dense (the
@@ -1140,6 +1181,7 @@ jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats
   float ms_tr = 0.f;
   for (int it = 1; it <= c->cfg.max_transport_iterations; ++it) {
     c->stats.n_iterations = it;
+    NvtxRange loop_range("Jaybenne::TransportLoop");
     cudaEventRecord(c->ev[2], c->stream);
     s = transport_range(c, first, c->n - first, t_start, dt);
     if (s != JB_OK) return s;
@@ -1302,8 +1344,13 @@ jb_status jb_set_particles(jb_ctx *c, const jb_particles *s, int64_t n) {
     int ijk[3] = {0, 0, 0};
     const double pos[3] = {s->x[m], s->y ? s->y[m] : 0.0, s->z ? s->z[m] : 0.0};
     for (int d = 0; d < c->mesh.ndim; ++d) {
+      // the DBlock's own dx (set_mesh) so the index is what Xtoijk returns on the device; the transport
+      // kernels trust the stored cell, so a position on or outside the block edge is refused here
       const double dxd = (B.xmax[d] - B.xmin[d]) / c->mesh.nxb[d];
       ijk[d] = static_cast<int>(std::floor((pos[d] - B.xmin[d]) / dxd));
+      if (ijk[d] < 0 || ijk[d] >= c->mesh.nxb[d])
+        return fail(c, JB_ERR_INVALID, "jb_set_particles: particle " + std::to_string(m) + " lies outside block " +
+                                           std::to_string(gid) + " (or on its upper edge)");
     }
     loc[m] = make_int2(c->gid_to_local[gid], (ijk[2] * c->mesh.nxb[1] + ijk[1]) * c->mesh.nxb[0] + ijk[0]);
     a[m] = s->rng ? make_uint2(s->rng[4 * m], s->rng[4 * m + 1]) : make_uint2((uint32_t)m, (uint32_t)gid);
@@ -1399,7 +1446,9 @@ jb_status jb_exchange_give_device(jb_ctx *c, const void *dev_ptr, int64_t n_reco
   if (c->n + n_records > c->capacity) {
     if (c->requested_capacity > 0 && c->n + n_records > c->requested_capacity)
       return fail(c, JB_ERR_CAPACITY, "photon pool capacity exceeded on receive");
-    jb_status s = ensure_capacity(c, c->n + n_records);
+    // grow the swarm arrays only: the outbox (records other peers have not taken yet, device pointers a host
+    // program got from jb_exchange_take_device) and the inbox stay where they are
+    jb_status s = c->out.rec ? grow_pool_only(c, c->n + n_records) : ensure_capacity(c, c->n + n_records);
     if (s != JB_OK) return s;
   }
   StepParams P = make_params(c);
