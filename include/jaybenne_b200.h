@@ -260,6 +260,10 @@ jb_status jb_set_particles(jb_ctx *ctx, const jb_particles *src, int64_t n);
  * source call): a run repeated on the same inputs after this call reproduces the same photons. The
  * reference's pool generator has no counterpart (its streams depend on the thread schedule). */
 jb_status jb_reset_streams(jb_ctx *ctx);
+/* how the last multi-rank jb_radiation_step moved photons between ranks: 0 = single rank / not yet run,
+ * 1 = count all-gather + grouped ncclSend / ncclRecv per iteration, 2 = direct stores into the peers'
+ * IPC-mapped inboxes over NVLink with the loop state on the device (needs jb_set_capacity; JB_P2P=0 disables) */
+int32_t jb_exchange_mode(const jb_ctx *ctx);
 /* change jb_config::sort_interval of a live context (0 = never sort the pool by (meshblock, cell)) */
 jb_status jb_set_sort_interval(jb_ctx *ctx, int32_t every_n_cycles);
 /* cumulative stats since the last jb_radiation_step / jb_stats_begin began */

@@ -164,6 +164,7 @@ DEVICE_API = {
     "exchange_give_device": (C.c_int, [ctx_p, C.c_void_p, C.c_int64]),
     "exchange_clear": (C.c_int, [ctx_p]),
     "set_sort_interval": (C.c_int, [ctx_p, C.c_int32]),
+    "exchange_mode": (C.c_int32, [ctx_p]),
     "set_remote_field": (C.c_int, [ctx_p, C.c_int32, C.c_int32, C.c_void_p]),
     "set_fields": (C.c_int, [ctx_p, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_void_p)]),
     "get_fields": (C.c_int, [ctx_p, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_void_p)]),

@@ -238,7 +238,7 @@ class Mcblock {
     const std::string hst_path = opt_.outdir + "/" + problem_id_ + ".hst.r" + std::to_string(rank_) + ".csv";
     std::ofstream hst(hst_path);
     hst << "cycle,time,dt,n_start,n_sourced,n_absorbed,n_escaped,n_end,n_sent,n_received,n_block_crossings,n_segments,"
-           "n_scatters,n_ddmc_segments,n_iterations,e_start,e_sourced,e_absorbed,e_escaped,e_end,ms_transport,ms_total\n";
+           "n_scatters,n_ddmc_segments,n_bface_resampled,n_iterations,e_start,e_sourced,e_absorbed,e_escaped,e_end,ms_transport,ms_total\n";
     hst.precision(17);
     Real next_out = out_dt_ > 0 ? out_dt_ : std::numeric_limits<Real>::infinity();
     if (out_dt_ > 0) Dump(0);
@@ -248,7 +248,7 @@ class Mcblock {
       const jb_cycle_stats s = Step();
       hst << ncycle_ << ',' << time_ << ',' << dt_ << ',' << s.n_start << ',' << s.n_sourced << ',' << s.n_absorbed << ','
           << s.n_escaped << ',' << s.n_end << ',' << s.n_sent << ',' << s.n_received << ',' << s.n_block_crossings << ','
-          << s.n_segments << ',' << s.n_scatters << ',' << s.n_ddmc_segments << ',' << s.n_iterations << ',' << s.e_start
+          << s.n_segments << ',' << s.n_scatters << ',' << s.n_ddmc_segments << ',' << s.n_bface_resampled << ',' << s.n_iterations << ',' << s.e_start
           << ',' << s.e_sourced << ',' << s.e_absorbed << ',' << s.e_escaped << ',' << s.e_end << ',' << s.ms_transport
           << ',' << s.ms_total << '\n';
       if (rank_ == 0 && !opt_.quiet)

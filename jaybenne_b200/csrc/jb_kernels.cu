@@ -383,18 +383,21 @@ __global__ void __launch_bounds__(256, 4) k_source_emit(StepParams P, int first_
   const DMesh &m = P.mesh;
   const double vv = P.cl.c_code, sb = P.cl.sb_code;
   const int lane = threadIdx.x & 31;
-  const long long warp0 = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
-  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  // 32-bit cell arithmetic: a rank holds < 2^31 cells (checked by the launcher), and the 64-bit divide /
+  // modulo this loop used to do per cell were ~1/3 of the kernel's instructions (profiles/r02_ncu_source_emit*.md)
+  const unsigned warp0 = (unsigned)((blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5);
+  const unsigned nwarps = (unsigned)(((long long)gridDim.x * blockDim.x) >> 5);
+  const unsigned ncell_u = (unsigned)m.ncell, ncells_u = (unsigned)ncells;
   unsigned long long my_n = 0;
   double my_e = 0.0;
-  for (long long q = warp0; q < ncells; q += nwarps) {
-    const int lbq = (int)(q / m.ncell);
+  for (unsigned q = warp0; q < ncells_u; q += nwarps) {
+    const int lbq = (int)(q / ncell_u);
     const int lb = first_local + lbq;
-    const int ci = (int)(q % m.ncell);
+    const int ci = (int)(q - (unsigned)lbq * ncell_u);
     const long long c = (long long)lb * m.ncell + ci;
     const int npart = (int)round(P.f.src_num[c]);
     const long long pglobal = prefix[q];
-    const long long pblock = prefix[(long long)lbq * m.ncell];
+    const long long pblock = prefix[(unsigned)lbq * ncell_u];
     const int pstart = (int)(pglobal - pblock);
     const double ew = P.f.src_ew[c];
     if (lane == 0) {
@@ -885,6 +888,10 @@ void launch_transport(const StepParams &P, long long first, long long n, double 
 template <int NDIM>
 __global__ void k_bface(StepParams P, long long first, long long n) {
   const DMesh &m = P.mesh;
+  if (P.range) {
+    first = P.range[0];
+    n = P.range[1];
+  }
   for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < n;
        q += (long long)gridDim.x * blockDim.x) {
     const long long idx = first + q;
@@ -977,45 +984,61 @@ void launch_source_emit(const StepParams &P, int first_local, int nlocal_call, i
 // same cell: runs of equal cells inside a warp are summed with a segmented shuffle scan and
 // issue one atomic per run. A warp whose lanes are spread over many cells (after transport)
 // sees few equal neighbours in its ballot and takes the plain one-atomic-per-lane path.
-__global__ void k_tally(StepParams P, long long n, unsigned long long *n_alive) {
+__global__ void __launch_bounds__(256) k_tally(StepParams P, long long n, unsigned long long *n_alive) {
   const DMesh &m = P.mesh;
   unsigned long long a = 0;  // census totals ride along: photons in use and the energy they carry
   double e = 0.0;
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31u;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  const long long n_round = ((n + 31) / 32) * 32;  // whole warps stay in the loop together
-  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < n_round; idx += stride) {
-    long long cell = -1;
-    double v = 0.0;
-    if (idx < n) {
-      const int2 lc = P.s.loc[idx];
-      if (lc.x >= 0) {
-        const DBlock &b = m.blocks[m.local_gid[lc.x]];
-        const double dv = b.dx[0] * b.dx[1] * b.dx[2];
-        cell = (long long)lc.x * m.ncell + lc.y;
-        const double ww = P.s.w[idx];
-        v = ww / dv;
-        a++;
-        e += ww;
-      }
-    }
-    const long long prev = __shfl_up_sync(FULL, cell, 1);
-    const bool head = lane == 0 || prev != cell;
-    const unsigned heads = __ballot_sync(FULL, head);
-    if (__popc(heads) > 16) {  // mostly distinct cells: aggregation would not pay
-      if (cell >= 0) atomicAdd(&P.f.tally[cell], v);
-      continue;
-    }
-    // segmented inclusive scan towards higher lanes; the last lane of each run holds the run's sum
-    const unsigned seg_start = 31u - __clz(heads & ((2u << lane) - 1u));  // first lane of my run
+  // Each warp takes TALLY_U consecutive groups of 32 slots per trip and requests all of their loads (cell and
+  // weight) before it looks at any: the kernel is a 16 B / photon stream whose only enemy is load latency
+  // (profiles/r02_ncu_tally*.md: 13 of 20 cycles per issue on the long scoreboard with one group in flight).
+  constexpr int TALLY_U = 4;
+  const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  const long long ngroups = (n + 31) / 32;
+  for (long long g0 = warp * TALLY_U; g0 < ngroups; g0 += nwarps * TALLY_U) {
+    int2 lc[TALLY_U];
+    double ww[TALLY_U];
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const double up = __shfl_up_sync(FULL, v, o);
-      if (lane >= seg_start + o) v += up;
+    for (int u = 0; u < TALLY_U; ++u) {
+      const long long idx = (g0 + u) * 32 + lane;
+      const bool in = idx < n;
+      lc[u] = in ? __ldcs(&P.s.loc[idx]) : make_int2(-1, 0);
+      ww[u] = in ? __ldcs(&P.s.w[idx]) : 0.0;
     }
-    const bool tail = lane == 31u || ((heads >> (lane + 1)) & 1u);
-    if (tail && cell >= 0) atomicAdd(&P.f.tally[cell], v);
+#pragma unroll
+    for (int u = 0; u < TALLY_U; ++u) {
+      if (g0 + u >= ngroups) break;  // warp-uniform
+      long long cell = -1;
+      double v = 0.0;
+      if (lc[u].x >= 0) {
+        // cell volume of the photon's block: dx pairs of the 64-byte geometry line (same product, same order,
+        // as coords.Volume: dx1 * dx2 * dx3)
+        const BlkGeo *geo = m.geo + __ldg(&m.local_gid[lc[u].x]);
+        const double dv = __ldg(&geo->xd[0]).y * __ldg(&geo->xd[1]).y * __ldg(&geo->xd[2]).y;
+        cell = (long long)lc[u].x * m.ncell + lc[u].y;
+        v = ww[u] / dv;
+        a++;
+        e += ww[u];
+      }
+      const long long prev = __shfl_up_sync(FULL, cell, 1);
+      const bool head = lane == 0 || prev != cell;
+      const unsigned heads = __ballot_sync(FULL, head);
+      if (__popc(heads) > 16) {  // mostly distinct cells: aggregation would not pay
+        if (cell >= 0) atomicAdd(&P.f.tally[cell], v);
+        continue;
+      }
+      // segmented inclusive scan towards higher lanes; the last lane of each run holds the run's sum
+      const unsigned seg_start = 31u - __clz(heads & ((2u << lane) - 1u));  // first lane of my run
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const double up = __shfl_up_sync(FULL, v, o);
+        if (lane >= seg_start + o) v += up;
+      }
+      const bool tail = lane == 31u || ((heads >> (lane + 1)) & 1u);
+      if (tail && cell >= 0) atomicAdd(&P.f.tally[cell], v);
+    }
   }
   warp_add_u64(n_alive, a);
   warp_add_energy(P, EB_CENSUS, e);
@@ -1024,7 +1047,7 @@ void launch_tally(const StepParams &P, long long n, unsigned long long *n_alive,
   const long long ncells = (long long)P.mesh.nlocal * P.mesh.ncell;
   cudaMemsetAsync(P.f.tally, 0, sizeof(double) * ncells, st);
   cudaMemsetAsync(P.ebins + EB_CENSUS * EBINS, 0, sizeof(double) * EBINS, st);
-  if (n > 0) k_tally<<<grid_for(n, 256), 256, 0, st>>>(P, n, n_alive);
+  if (n > 0) k_tally<<<grid_for((n + 3) / 4, 256), 256, 0, st>>>(P, n, n_alive);
   launch_fold_bins(P, EB_CENSUS, e_sum, st);
 }
 
@@ -1158,7 +1181,8 @@ void launch_compact(const StepParams &P, long long n, long long n_alive, long lo
 // ---------------------------------------------------------------------------------------
 // Receive side of the swarm exchange: append records to the pool (Swarm::Receive).
 // ---------------------------------------------------------------------------------------
-__global__ void k_unpack(StepParams P, const ExRecord *rec, long long nrec, long long slot0, double t_end) {
+__device__ __forceinline__ void unpack_records(const StepParams &P, const ExRecord *rec, long long nrec, long long slot0,
+                                               double t_end) {
   const DMesh &m = P.mesh;
   unsigned long long c_unf = 0, c_err = 0, c_rcv = 0;
   for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < nrec;
@@ -1189,6 +1213,9 @@ __global__ void k_unpack(StepParams P, const ExRecord *rec, long long nrec, long
   warp_add_u64(&P.stats->n_received, c_rcv);
   warp_add_u64(&P.stats->n_unfinished, c_unf);
   warp_add_u64(&P.stats->n_error, c_err);
+}
+__global__ void k_unpack(StepParams P, const ExRecord *rec, long long nrec, long long slot0, double t_end) {
+  unpack_records(P, rec, nrec, slot0, t_end);
 }
 void launch_unpack(const StepParams &P, const ExRecord *rec, long long nrec, long long slot0, double t_end,
                    cudaStream_t st) {
@@ -1282,4 +1309,144 @@ void launch_selftest_division(long long n, unsigned long long *mismatches, cudaS
 void launch_fp64_chain(double *sink, int iters, int blocks, cudaStream_t st) {
   k_fp64_chain<<<blocks, 256, 0, st>>>(sink, iters);
 }
+
+// ---------------------------------------------------------------------------------------
+// Direct peer exchange over NVLink: replaces the count all-gather + host synchronisation + grouped
+// ncclSend/ncclRecv of one transport iteration (jaybenne.cpp:26-61, 113-131 in the reference: swarm
+// Send / Receive + CheckCompletion) by stores into the peers' mapped inboxes and flags, so the host
+// can queue several iterations without waiting for any of them.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// one CTA: reserve a range of every peer's inbox for this iteration's records
+__global__ void k_p2p_reserve(StepParams P, P2PState *st, const P2PPeers *peers, int R, long long inbox_cap) {
+  const int r = threadIdx.x;
+  if (r >= R) return;
+  unsigned long long cnt = 0, base = 0;
+  if (!st->done && r != P.mesh.my_rank) {
+    cnt = P.out.count[r];
+    if ((long long)cnt > P.out.cap) cnt = (unsigned long long)P.out.cap;  // the overflow itself is counted by the kernels
+    if (cnt) {
+      const int par = (int)(st->epoch & 1ull);
+      base = atomicAdd_system(&peers->mail[r]->inbox_count[par], cnt);
+      if ((long long)(base + cnt) > inbox_cap) {  // receiver's inbox is full: send what fits, flag the rest
+        atomicOr(&st->error, 1);
+        cnt = (long long)base < inbox_cap ? (unsigned long long)inbox_cap - base : 0ull;
+      }
+    }
+  }
+  st->cnt[r] = cnt;
+  st->base[r] = base;
+}
+// blockIdx.y = peer: copy my outbox segment for that peer into its inbox, 16 bytes per thread and trip
+__global__ void k_p2p_copy(StepParams P, const P2PState *st, const P2PPeers *peers) {
+  const int r = blockIdx.y;
+  const unsigned long long cnt = st->cnt[r];
+  if (cnt == 0) return;
+  const int par = (int)(st->epoch & 1ull);
+  const uint4 *src = reinterpret_cast<const uint4 *>(P.out.rec + (size_t)r * P.out.cap);
+  uint4 *dst = reinterpret_cast<uint4 *>(peers->inbox[par][r] + st->base[r]);
+  const unsigned long long nq = cnt * (sizeof(ExRecord) / sizeof(uint4));
+  for (unsigned long long q = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; q < nq;
+       q += (unsigned long long)gridDim.x * blockDim.x)
+    dst[q] = src[q];
+  __threadfence_system();  // the records are visible to the peer before the flag of k_p2p_signal can be
+}
+// one CTA: tell every rank how much I sent in total and that my records for it have landed
+__global__ void k_p2p_signal(StepParams P, P2PState *st, const P2PPeers *peers, int R) {
+  __shared__ unsigned long long total;
+  const int r = threadIdx.x;
+  if (r == 0) {
+    unsigned long long t = 0;
+    for (int q = 0; q < R; ++q) t += st->cnt[q];
+    total = t;
+  }
+  __syncthreads();
+  if (r >= R) return;
+  if (st->done) return;
+  const unsigned long long epoch = st->epoch;
+  const int par = (int)(epoch & 1ull);
+  P.out.count[r] = 0ull;  // my outbox is empty again
+  __threadfence_system();
+  P2PMail *mail = peers->mail[r];
+  *reinterpret_cast<volatile unsigned long long *>(&mail->sent[par][P.mesh.my_rank]) = total;
+  __threadfence_system();
+  st_release_sys(&mail->arrive[P.mesh.my_rank], epoch + 1ull);
+}
+// one CTA: wait until every rank's records for me have landed, then advance the loop state
+__global__ void k_p2p_wait(StepParams P, P2PState *st, P2PMail *mine, int R, long long inbox_cap) {
+  __shared__ int timed_out;
+  const int r = threadIdx.x;
+  if (r == 0) timed_out = 0;
+  __syncthreads();
+  if (st->done) return;
+  const unsigned long long epoch = st->epoch;
+  const int par = (int)(epoch & 1ull);
+  if (r < R) {
+    const long long t0 = clock64();
+    while (ld_acquire_sys(&mine->arrive[r]) < epoch + 1ull) {
+      if (clock64() - t0 > 20000000000LL) {  // ~10 s: a peer died; fail the step instead of hanging the GPU
+        timed_out = 1;
+        break;
+      }
+      __nanosleep(200);
+    }
+  }
+  __syncthreads();
+  if (r != 0) return;
+  unsigned long long total = 0;
+  for (int q = 0; q < R; ++q) total += *reinterpret_cast<volatile unsigned long long *>(&mine->sent[par][q]);
+  unsigned long long nrecv = *reinterpret_cast<volatile unsigned long long *>(&mine->inbox_count[par]);
+  mine->inbox_count[par] = 0ull;  // nobody touches this parity again before my next-but-one signal
+  if (timed_out) atomicOr(&st->error, 4);
+  if ((long long)nrecv > inbox_cap) {
+    nrecv = (unsigned long long)inbox_cap;
+    atomicOr(&st->error, 1);
+  }
+  if (st->n + (long long)nrecv > st->capacity) {
+    atomicOr(&st->error, 2);
+    nrecv = (unsigned long long)(st->capacity - st->n);
+  }
+  st->range[0] = st->n;
+  st->range[1] = (long long)nrecv;
+  st->n += (long long)nrecv;
+  st->parity = par;
+  st->sent_last = total;
+  st->iterations += 1;
+  st->done = (total == 0ull || timed_out) ? 1 : 0;
+  st->epoch = epoch + 1ull;
+}
+__global__ void k_p2p_unpack(StepParams P, const P2PState *st, const ExRecord *inbox0, const ExRecord *inbox1, double t_end) {
+  const long long nrec = st->range[1];
+  if (nrec <= 0) return;
+  unpack_records(P, st->parity ? inbox1 : inbox0, nrec, st->range[0], t_end);
+}
+
+void launch_p2p_push(const StepParams &P, P2PState *state, const P2PPeers *peers, int n_ranks, long long inbox_cap,
+                     cudaStream_t st) {
+  k_p2p_reserve<<<1, P2P_MAX_RANKS, 0, st>>>(P, state, peers, n_ranks, inbox_cap);
+  k_p2p_copy<<<dim3(32, (unsigned)n_ranks), 256, 0, st>>>(P, state, peers);
+  k_p2p_signal<<<1, P2P_MAX_RANKS, 0, st>>>(P, state, peers, n_ranks);
+}
+void launch_p2p_wait_unpack(const StepParams &P, P2PState *state, P2PMail *my_mail, ExRecord *inbox0, ExRecord *inbox1,
+                            int n_ranks, long long inbox_cap, double t_end, bool ddmc, cudaStream_t st) {
+  k_p2p_wait<<<1, P2P_MAX_RANKS, 0, st>>>(P, state, my_mail, n_ranks, inbox_cap);
+  k_p2p_unpack<<<148, 128, 0, st>>>(P, state, inbox0, inbox1, t_end);
+  if (ddmc && P.mesh.ndim >= 2) {
+    StepParams Q = P;
+    Q.range = state->range;  // address of the device-side (first, n)
+    if (P.mesh.ndim == 2)
+      k_bface<2><<<148, 128, 0, st>>>(Q, 0, 0);
+    else
+      k_bface<3><<<148, 128, 0, st>>>(Q, 0, 0);
+  }
+}
+
 }  // namespace jbd

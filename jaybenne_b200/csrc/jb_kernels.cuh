@@ -89,6 +89,31 @@ struct Outbox {
   long long cap;
 };
 
+// ---- direct peer exchange over NVLink (jb_lib.cu: p2p_*) -------------------------------------------
+// One mailbox per rank, in that rank's device memory and mapped by every peer (CUDA IPC). A sender
+// reserves a range of the receiver's inbox with one system-scope atomicAdd per peer and iteration,
+// copies its outbox segment there with plain stores over NVLink, then publishes `sent` and `arrive`.
+// Inboxes and their counters are double-buffered by iteration parity: a peer can be one iteration ahead.
+static constexpr int P2P_MAX_RANKS = 64;
+struct P2PMail {
+  unsigned long long inbox_count[2];            // records reserved in inbox[parity] (remote atomics)
+  unsigned long long arrive[P2P_MAX_RANKS];     // arrive[src] = last epoch src finished pushing to me
+  unsigned long long sent[2][P2P_MAX_RANKS];    // sent[parity][src] = records src sent to ALL ranks that epoch
+};
+struct P2PPeers {                               // device table of the mapped peer pointers
+  ExRecord *inbox[2][P2P_MAX_RANKS];
+  P2PMail *mail[P2P_MAX_RANKS];
+};
+struct P2PState {                               // this rank's loop state, device resident: no host round trips
+  long long range[2];                           // (first, n) of the next transport launch = the arrivals
+  long long n, capacity;                        // pool size and limit
+  unsigned long long epoch;                     // iteration counter across the whole run (never reset)
+  unsigned long long sent_last;                 // records ALL ranks sent in the last iteration
+  int done, iterations, error, parity;          // error: 1 inbox overflow, 2 pool overflow, 4 peer timed out
+  unsigned long long base[P2P_MAX_RANKS];       // reservation results of the current push
+  unsigned long long cnt[P2P_MAX_RANKS];        // records to push per peer (outbox counts, clamped)
+};
+
 // counters accumulated on the device during one radiation step
 struct DStats {
   unsigned long long n_sourced, n_absorbed, n_escaped, n_sent, n_received, n_crossings;
@@ -124,6 +149,7 @@ struct StepParams {
   DStats *stats;
   double *ebins;  // [EB_KINDS][EBINS]
   unsigned long long *work;  // chunk counter of the persistent transport kernel (zero at launch)
+  const long long *range;    // non-null: the kernel reads (first, n) here (P2PState::range) instead of its arguments
   uint32_t key0, key1_particle, key1_cell;
   int use_ddmc;
   double tau_ddmc;
@@ -150,7 +176,9 @@ struct TransportTuning {
   int validate;     // 1: cross-check the face-crossing index update against Xtoijk (n_error)
 };
 void set_transport_tuning(const TransportTuning &t);
+bool transport_takes_device_range(const StepParams &P);
 void set_pool_tuning(int slots, int refill_min, int ready_low);
+void set_pool_prefetch(int on);
 void launch_pack_props(const StepParams &P, cudaStream_t st);
 // folds ebins[kind] into *dst (dst = &stats->e_* or the census scratch)
 void launch_fold_bins(const StepParams &P, int kind, double *dst, cudaStream_t st);
@@ -167,6 +195,11 @@ void launch_unpack(const StepParams &P, const ExRecord *rec, long long nrec, lon
                    cudaStream_t st);
 void launch_bface(const StepParams &P, long long n, cudaStream_t st);
 void launch_bface_range(const StepParams &P, long long first, long long n, cudaStream_t st);
+// direct peer exchange: one iteration = push (reserve + copy + signal), wait, unpack [+ bface], all on `st`
+void launch_p2p_push(const StepParams &P, P2PState *state, const P2PPeers *peers, int n_ranks, long long inbox_cap,
+                     cudaStream_t st);
+void launch_p2p_wait_unpack(const StepParams &P, P2PState *state, P2PMail *my_mail, ExRecord *inbox0, ExRecord *inbox1,
+                            int n_ranks, long long inbox_cap, double t_end, bool ddmc, cudaStream_t st);
 // cell sort: key = blk * ncell + cell
 void launch_sort_keys(const StepParams &P, long long n, int *cell_count, cudaStream_t st);
 void launch_sort_perm(const StepParams &P, long long n, long long *cell_offset, unsigned int *perm, cudaStream_t st);

@@ -112,6 +112,17 @@ struct jb_ctx {
   long long inbox_cap = 0;
   unsigned long long *d_count_matrix = nullptr;
   ncclComm_t comm = nullptr;
+  // direct peer exchange over NVLink (p2p_setup): IPC-mapped inboxes + mailboxes, device-resident loop state
+  bool p2p_tried = false, p2p_on = false;
+  int exchange_mode = 0;               // what the last multi-rank step used (jb_exchange_mode)
+  P2PMail *d_mail = nullptr;
+  ExRecord *d_p2p_inbox[2] = {nullptr, nullptr};
+  long long p2p_inbox_cap = 0;
+  P2PState *d_p2p_state = nullptr;
+  P2PState *h_p2p_state = nullptr;     // pinned
+  P2PPeers *d_peers = nullptr;
+  std::vector<void *> ipc_opened;      // peer mappings to close
+  cudaEvent_t it_ev[2 * 16] = {};      // transport launch brackets of the queued iterations
   // event log
   jb_event *d_events = nullptr;
   long long event_cap = 0;
@@ -369,6 +380,7 @@ jb_status jb_create(const jb_config *cfg, jb_ctx **out) {
       if (const char *v = getenv("JB_POOL_REFILL_MIN")) prf = atoi(v);
       if (const char *v = getenv("JB_POOL_READY_LOW")) prl = atoi(v);
       set_pool_tuning(ps, prf, prl);
+      if (const char *v = getenv("JB_POOL_PREFETCH")) set_pool_prefetch(atoi(v));
     }
   }
   *out = c;
@@ -379,6 +391,11 @@ void jb_destroy(jb_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
+  for (void *q : c->ipc_opened) cudaIpcCloseMemHandle(q);
+  dfree(c->d_mail); dfree(c->d_p2p_inbox[0]); dfree(c->d_p2p_inbox[1]); dfree(c->d_p2p_state); dfree(c->d_peers);
+  if (c->h_p2p_state) cudaFreeHost(c->h_p2p_state);
+  for (auto &e : c->it_ev)
+    if (e) cudaEventDestroy(e);
   if (c->comm && nccl_api().ok) nccl_api().CommDestroy(c->comm);
   free_swarm(c);
   dfree(c->d_blocks); dfree(c->d_lattice); dfree(c->d_local_gid); dfree(c->d_nbr); dfree(c->d_geo);
@@ -472,6 +489,8 @@ jb_status jb_set_mesh(jb_ctx *c, const jb_mesh *m, int32_t my_rank, int32_t n_ra
   const long long nc = (long long)m->nxb[0] * m->nxb[1] * m->nxb[2];
   const long long nl = (long long)c->local_gid.size();
   c->ncells_local = nc * nl;
+  if (c->ncells_local >= 0x7fffffffLL)
+    return fail(c, JB_ERR_CAPACITY, "more than 2^31 cells on one rank (the sourcing kernels index cells with 32 bits)");
   JB_CUDA(c, dalloc(&c->d_blocks, m->nblocks));
   JB_CUDA(c, dalloc(&c->d_lattice, (long long)lattice.size()));
   JB_CUDA(c, dalloc(&c->d_local_gid, nl));
@@ -1156,6 +1175,148 @@ jb_status jb_get_stats(jb_ctx *c, jb_cycle_stats *out) {
   return JB_OK;
 }
 
+// ---- direct peer exchange over NVLink ---------------------------------------------------------------
+// Set up once, collectively, at the first multi-rank step of a context with a fixed pool (jb_set_capacity):
+// every rank allocates a mailbox and two inboxes, the CUDA IPC handles travel through one ncclAllGather, and
+// every rank maps every peer's. Any failure on any rank (no peer access, JB_P2P=0, IPC refused) leaves ALL
+// ranks on the NCCL send/recv path: the verdict is all-reduced.
+__global__ void k_p2p_begin(P2PState *st, long long n, long long capacity) {
+  st->n = n;
+  st->capacity = capacity;
+  st->range[0] = 0;
+  st->range[1] = 0;
+  st->done = 0;
+  st->iterations = 0;
+  st->error = 0;
+  st->sent_last = 0;
+}
+static jb_status p2p_setup(jb_ctx *c) {
+  c->p2p_tried = true;
+  NcclApi &nc = nccl_api();
+  const int R = c->n_ranks;
+  int ok = 1;
+  if (const char *v = getenv("JB_P2P")) ok = atoi(v) != 0;
+  if (R > P2P_MAX_RANKS || c->requested_capacity <= 0 || !c->out.rec) ok = 0;
+  struct Handles { cudaIpcMemHandle_t mail, in0, in1; };
+  static_assert(sizeof(Handles) == 192, "three 64-byte handles");
+  Handles mine;
+  memset(&mine, 0, sizeof(mine));
+  if (ok) {
+    c->p2p_inbox_cap = 2 * c->out.cap;
+    ok = dalloc(&c->d_mail, 1) == cudaSuccess && dalloc(&c->d_p2p_inbox[0], c->p2p_inbox_cap) == cudaSuccess &&
+         dalloc(&c->d_p2p_inbox[1], c->p2p_inbox_cap) == cudaSuccess && dalloc(&c->d_p2p_state, 1) == cudaSuccess &&
+         dalloc(&c->d_peers, 1) == cudaSuccess &&
+         cudaMallocHost((void **)&c->h_p2p_state, sizeof(P2PState)) == cudaSuccess;
+    if (ok) {
+      cudaMemset(c->d_mail, 0, sizeof(P2PMail));
+      cudaMemset(c->d_p2p_state, 0, sizeof(P2PState));
+      ok = cudaIpcGetMemHandle(&mine.mail, c->d_mail) == cudaSuccess &&
+           cudaIpcGetMemHandle(&mine.in0, c->d_p2p_inbox[0]) == cudaSuccess &&
+           cudaIpcGetMemHandle(&mine.in1, c->d_p2p_inbox[1]) == cudaSuccess;
+    }
+    cudaGetLastError();
+  }
+  // all ranks take part in the two collectives whatever their local verdict
+  unsigned char *d_h = nullptr;
+  JB_CUDA(c, dalloc(&d_h, (long long)192 * (R + 1) + 64));
+  std::vector<Handles> all((size_t)R);
+  JB_CUDA(c, cudaMemcpy(d_h + (size_t)192 * R, &mine, 192, cudaMemcpyHostToDevice));
+  bool comm_ok = nc.AllGather(d_h + (size_t)192 * R, d_h, 192, ncclUint8, c->comm, c->stream) == ncclSuccess;
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  JB_CUDA(c, cudaMemcpy(all.data(), d_h, (size_t)192 * R, cudaMemcpyDeviceToHost));
+  P2PPeers peers;
+  memset(&peers, 0, sizeof(peers));
+  if (ok && comm_ok) {
+    for (int r = 0; r < R && ok; ++r) {
+      if (r == c->my_rank) {
+        peers.mail[r] = c->d_mail;
+        peers.inbox[0][r] = c->d_p2p_inbox[0];
+        peers.inbox[1][r] = c->d_p2p_inbox[1];
+        continue;
+      }
+      void *pm = nullptr, *p0 = nullptr, *p1 = nullptr;
+      ok = cudaIpcOpenMemHandle(&pm, all[r].mail, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess &&
+           cudaIpcOpenMemHandle(&p0, all[r].in0, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess &&
+           cudaIpcOpenMemHandle(&p1, all[r].in1, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+      for (void *q : {pm, p0, p1})
+        if (q) c->ipc_opened.push_back(q);
+      peers.mail[r] = (P2PMail *)pm;
+      peers.inbox[0][r] = (ExRecord *)p0;
+      peers.inbox[1][r] = (ExRecord *)p1;
+    }
+    cudaGetLastError();
+  }
+  int *d_ok = reinterpret_cast<int *>(d_h + (size_t)192 * (R + 1));
+  int h_ok = (ok && comm_ok) ? 1 : 0;
+  JB_CUDA(c, cudaMemcpy(d_ok, &h_ok, sizeof(int), cudaMemcpyHostToDevice));
+  comm_ok = nc.AllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, c->comm, c->stream) == ncclSuccess && comm_ok;
+  JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  JB_CUDA(c, cudaMemcpy(&h_ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost));
+  cudaFree(d_h);
+  if (!comm_ok) return fail(c, JB_ERR_COMM, "NCCL failed while exchanging the peer-memory handles");
+  c->p2p_on = h_ok == 1;
+  if (c->p2p_on) {
+    JB_CUDA(c, cudaMemcpy(c->d_peers, &peers, sizeof(peers), cudaMemcpyHostToDevice));
+    for (auto &e : c->it_ev) JB_CUDA(c, cudaEventCreate(&e));
+  }
+  return JB_OK;
+}
+
+// The transport / exchange iterations of one cycle with the exchange done by the GPUs themselves: the host
+// queues P2P_CHUNK iterations (transport of the arrivals, push to the peers, wait for theirs, unpack) and looks
+// at the device-resident loop state once per chunk. An iteration after the one in which no rank sent anything
+// finds an empty range and a set `done` flag and costs a few empty launches.
+static constexpr int P2P_CHUNK = 12;
+static jb_status transport_iterations_p2p(jb_ctx *c, double t_start, double dt, float *ms_tr) {
+  k_p2p_begin<<<1, 1, 0, c->stream>>>(c->d_p2p_state, c->n, c->capacity);
+  c->launches += 1;
+  const bool ddmc = c->cfg.use_ddmc != 0;
+  int queued = 0;
+  for (;;) {
+    int in_chunk = 0;
+    for (int k = 0; k < P2P_CHUNK && queued < c->cfg.max_transport_iterations; ++k, ++queued, ++in_chunk) {
+      NvtxRange loop_range("Jaybenne::TransportLoop");
+      StepParams P = make_params(c);
+      if (c->props_dirty) {
+        launch_pack_props(P, c->stream);
+        c->launches += 1;
+        c->props_dirty = false;
+      }
+      c->census_valid = false;
+      JB_CUDA(c, cudaMemsetAsync(P.work, 0, sizeof(unsigned long long), c->stream));
+      cudaEventRecord(c->it_ev[2 * k], c->stream);
+      if (queued == 0) {
+        launch_transport(P, 0, c->n, t_start, dt, c->stream);  // the whole pool: the host knows its size
+      } else {
+        P.range = c->d_p2p_state->range;  // the arrivals: (first, n) on the device
+        launch_transport(P, 0, c->capacity, t_start, dt, c->stream);
+      }
+      cudaEventRecord(c->it_ev[2 * k + 1], c->stream);
+      P.range = nullptr;
+      launch_p2p_push(P, c->d_p2p_state, c->d_peers, c->n_ranks, c->p2p_inbox_cap, c->stream);
+      launch_p2p_wait_unpack(P, c->d_p2p_state, c->d_mail, c->d_p2p_inbox[0], c->d_p2p_inbox[1], c->n_ranks,
+                             c->p2p_inbox_cap, t_start + dt, ddmc, c->stream);
+      c->launches += 6 + (ddmc ? 1 : 0);
+    }
+    JB_CUDA(c, cudaMemcpyAsync(c->h_p2p_state, c->d_p2p_state, sizeof(P2PState), cudaMemcpyDeviceToHost, c->stream));
+    JB_CUDA(c, cudaStreamSynchronize(c->stream));
+    JB_CUDA(c, cudaGetLastError());
+    for (int k = 0; k < in_chunk; ++k) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, c->it_ev[2 * k], c->it_ev[2 * k + 1]);
+      *ms_tr += ms;
+    }
+    const P2PState &h = *c->h_p2p_state;
+    c->n = h.n;
+    c->stats.n_iterations = h.iterations;
+    if (h.error & 4) return fail(c, JB_ERR_COMM, "a peer did not deliver its records (direct peer exchange timed out)");
+    if (h.error & 1) return fail(c, JB_ERR_CAPACITY, "exchange inbox overflow: raise jb_set_capacity");
+    if (h.error & 2) return fail(c, JB_ERR_CAPACITY, "photon pool capacity exceeded on receive");
+    if (h.done) return JB_OK;
+    if (queued >= c->cfg.max_transport_iterations) return fail(c, JB_ERR_ITERATIONS, "max_transport_iterations exhausted");
+  }
+}
+
 // RadiationStep(...).Execute() (jaybenne.cpp:68-151)
 jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats *stats) {
   JB_REQUIRE_MESH(c);
@@ -1179,7 +1340,19 @@ jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats
   bool done = false;
   long long first = 0;
   float ms_tr = 0.f;
-  for (int it = 1; it <= c->cfg.max_transport_iterations; ++it) {
+  if (c->n_ranks > 1 && !c->p2p_tried) {
+    s = p2p_setup(c);
+    if (s != JB_OK) return s;
+  }
+  if (c->n_ranks > 1 && c->p2p_on && transport_takes_device_range(make_params(c))) {
+    c->exchange_mode = 2;
+    s = transport_iterations_p2p(c, t_start, dt, &ms_tr);
+    if (s != JB_OK) return s;
+    s = sync_stats(c);
+    if (s != JB_OK) return s;
+    done = true;
+  }
+  for (int it = 1; !done && it <= c->cfg.max_transport_iterations; ++it) {
     c->stats.n_iterations = it;
     NvtxRange loop_range("Jaybenne::TransportLoop");
     cudaEventRecord(c->ev[2], c->stream);
@@ -1197,6 +1370,7 @@ jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats
     }
     const long long n_before = c->n;
     long long total_sent = 0;
+    c->exchange_mode = 1;
     s = exchange_nccl(c, t_start + dt, &total_sent);
     if (s != JB_OK) return s;
     {
@@ -1295,6 +1469,8 @@ jb_status jb_get_particles(jb_ctx *c, const jb_particles *d, int64_t capacity, i
   }
   return JB_OK;
 }
+
+int32_t jb_exchange_mode(const jb_ctx *c) { return c ? c->exchange_mode : 0; }
 
 jb_status jb_set_sort_interval(jb_ctx *c, int32_t every_n_cycles) {
   if (!c || every_n_cycles < 0) return JB_ERR_INVALID;

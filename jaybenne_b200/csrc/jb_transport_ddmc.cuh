@@ -165,6 +165,10 @@ template <int NDIM, bool LOG, int MINB>
 __global__ void __launch_bounds__(IMC_TPB, MINB)
     k_transport_hybrid(StepParams P, long long first, long long n, double t_start, double dt, int refill_min) {
   const DMesh &m = P.mesh;
+  if (P.range) {
+    first = P.range[0];
+    n = P.range[1];
+  }
   constexpr bool multi_d = NDIM >= 2, three_d = NDIM == 3;
   const double t_end = t_start + dt;
   const double vv = P.cl.c_code;

@@ -198,6 +198,10 @@ template <int NDIM, int MINB, bool VALIDATE, int ABS>
 __global__ void __launch_bounds__(IMC_TPB, MINB)
     k_transport_imc(StepParams P, long long first, long long n, double t_start, double dt, int refill_min) {
   const DMesh &m = P.mesh;
+  if (P.range) {
+    first = P.range[0];
+    n = P.range[1];
+  }
   const double t_end = t_start + dt;
   const double vv = P.cl.c_code;
   const int nx1 = m.nxb[0], nx2 = m.nxb[1], nx3 = m.nxb[2];
@@ -496,6 +500,8 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
 
 static TransportTuning g_tuning = {2, 8, 4, 0};
 void set_transport_tuning(const TransportTuning &t) { g_tuning = t; }
+// the persistent kernels (variants 1, 2 and the hybrid kernel) can take their slot range from device memory
+bool transport_takes_device_range(const StepParams &P) { return g_tuning.variant >= 1 && P.log.cap <= 0; }
 
 template <int NDIM, int MINB, bool VALIDATE>
 static void launch_transport_imc_abs(const StepParams &P, long long first, long long n, double t_start, double dt,

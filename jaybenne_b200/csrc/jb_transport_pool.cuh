@@ -65,13 +65,17 @@ __device__ __forceinline__ int pool_pick(unsigned char *list, const unsigned m0,
 template <int NDIM, int MINB, bool VALIDATE, int ABS, int S>
 __global__ void __launch_bounds__(POOL_TPB, MINB)
     k_transport_pool(StepParams P, long long first, long long n, double t_start, double dt, int refill_min,
-                     int ready_low) {
+                     int ready_low, int l2_prefetch) {
   constexpr int NQ = ABS == ABS_GENERIC ? 3 : (ABS == ABS_GRAY_KIRCHHOFF ? 2 : 1);
   static_assert(S > 32 && S <= 64, "two slots per lane");
   __shared__ WarpPool<S, NQ> pools[POOL_WARPS];
   __shared__ unsigned sh_cnt[4];  // crossings, removed in the segment phase (escaped / sent / lost)
 
   const DMesh &m = P.mesh;
+  if (P.range) {  // direct peer exchange: the arrivals' range lives on the device (P2PState::range)
+    first = P.range[0];
+    n = P.range[1];
+  }
   const double t_end = t_start + dt;
   const double vv = P.cl.c_code;
   const int nx1 = m.nxb[0], nx2 = m.nxb[1], nx3 = m.nxb[2];
@@ -156,6 +160,17 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
           my32 = cur + lane;
           in_chunk = s >= 0 && my32 < end;
           cur = min(end, cur + (unsigned)cnt);
+          if (l2_prefetch && lane < 11u && cur < end) {
+            // the window the NEXT refill will read, pulled into L2 by the bulk-copy (TMA) unit while this
+            // one's photons run: one cp.async.bulk.prefetch.L2 per swarm array (16-byte aligned, 256 B)
+            const double *arr = lane == 0 ? P.s.x : lane == 1 ? P.s.y : lane == 2 ? P.s.z : lane == 3 ? P.s.t
+                              : lane == 4 ? P.s.vx : lane == 5 ? P.s.vy : lane == 6 ? P.s.vz : lane == 7 ? P.s.e
+                              : lane == 8 ? (const double *)P.s.loc : lane == 9 ? (const double *)P.s.ida
+                                                                                 : (const double *)P.s.idb;
+            const unsigned long long a0 = (unsigned long long)(arr + first + (long long)cur) & ~15ull;
+            const unsigned bytes = min(256u, ((end - cur) * 8u + 15u) & ~15u);
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a0), "r"(bytes) : "memory");
+          }
         }
       }
       int newst = PS_FREE;
@@ -425,8 +440,10 @@ struct PoolTuning {
   int slots;        // 56 (8 CTAs of 4 warps per SM) or 64 (7 CTAs)
   int refill_min;   // retire + refill when this many slots of a warp hold no live photon
   int ready_low;    // scatter early when fewer READY photons than this remain
+  int l2_prefetch;  // 1: cp.async.bulk.prefetch.L2 of the next refill window (JB_POOL_PREFETCH; measured)
 };
-static PoolTuning g_pool = {64, 24, 32};
+static PoolTuning g_pool = {64, 24, 32, 0};
+void set_pool_prefetch(int on) { g_pool.l2_prefetch = on ? 1 : 0; }
 void set_pool_tuning(int slots, int refill_min, int ready_low) {
   g_pool.slots = slots == 64 ? 64 : 56;
   g_pool.refill_min = max(1, min(refill_min, 32));
@@ -448,7 +465,7 @@ static void launch_transport_pool_abs(const StepParams &P, long long first, long
   const long long need = (n + (long long)POOL_WARPS * S - 1) / ((long long)POOL_WARPS * S);
   if (blocks > need) blocks = need;
   if (blocks < 1) blocks = 1;
-  const int rf = g_pool.refill_min, rl = g_pool.ready_low;
+  const int rf = g_pool.refill_min, rl = g_pool.ready_low, pf = g_pool.l2_prefetch;
   // MINB CTAs x 4 pools fill most of the SM's shared memory: ask for the largest carve-out once
   static bool carved = false;
   if (!carved) {
@@ -461,11 +478,11 @@ static void launch_transport_pool_abs(const StepParams &P, long long first, long
                          cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   }
   if (P.cl.opacity_model != JB_OPAC_GRAY)
-    k_transport_pool<NDIM, MINB, VALIDATE, ABS_GENERIC, S><<<(unsigned)blocks, POOL_TPB, 0, st>>>(P, first, n, t_start, dt, rf, rl);
+    k_transport_pool<NDIM, MINB, VALIDATE, ABS_GENERIC, S><<<(unsigned)blocks, POOL_TPB, 0, st>>>(P, first, n, t_start, dt, rf, rl, pf);
   else if (P.cl.gray_mode == JB_GRAY_DIRECT)
-    k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_DIRECT, S><<<(unsigned)blocks, POOL_TPB, 0, st>>>(P, first, n, t_start, dt, rf, rl);
+    k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_DIRECT, S><<<(unsigned)blocks, POOL_TPB, 0, st>>>(P, first, n, t_start, dt, rf, rl, pf);
   else
-    k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_KIRCHHOFF, S><<<(unsigned)blocks, POOL_TPB, 0, st>>>(P, first, n, t_start, dt, rf, rl);
+    k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_KIRCHHOFF, S><<<(unsigned)blocks, POOL_TPB, 0, st>>>(P, first, n, t_start, dt, rf, rl, pf);
 }
 // false: the range or the mesh does not fit the kernel's packed indices -> the caller takes k_transport_imc
 template <int NDIM>

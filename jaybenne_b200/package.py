@@ -264,6 +264,10 @@ class Jaybenne:
     def clear_particles(self):
         self._check(self.api.set_particles(self._ctx, None, 0))
 
+    def exchange_mode(self) -> int:
+        """0 none, 1 NCCL send/recv per iteration, 2 direct peer stores over NVLink (jb_exchange_mode)"""
+        return int(self.api.exchange_mode(self._ctx))
+
     def set_sort_interval(self, every_n_cycles: int):
         self._check(self.api.set_sort_interval(self._ctx, int(every_n_cycles)))
 

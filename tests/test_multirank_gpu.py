@@ -210,7 +210,9 @@ hist = []
 for _ in range({cycles}):
     hist.append(mb.Step())          # jb_radiation_step: NCCL exchange inside the library
     mb.time += mb.dt
-pickle.dump(T._collect(mb, hist), open(os.path.join({outdir!r}, "rank%d.pkl" % rank), "wb"))
+res = T._collect(mb, hist)
+res["exchange_mode"] = mb.jb.exchange_mode()
+pickle.dump(res, open(os.path.join({outdir!r}, "rank%d.pkl" % rank), "wb"))
 dist.barrier()
 dist.destroy_process_group()
 """
@@ -224,11 +226,15 @@ def _free_port():
     return p
 
 
+@pytest.mark.parametrize("p2p", ["1", "0"])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_nccl_ranks_equal_one_rank(world):
+def test_nccl_ranks_equal_one_rank(world, p2p, monkeypatch):
+    """JB_P2P=1 (default): photons travel by direct stores into the peers' IPC-mapped inboxes and the loop state
+    lives on the device; JB_P2P=0: count all-gather + grouped ncclSend / ncclRecv per iteration."""
     import torch
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
+    monkeypatch.setenv("JB_P2P", p2p)
     n, nb, ndim, cycles = 32, 8, 3, 2
     text = pu.synthetic_text(n=n, nb=nb, num_particles=200000, ndim=ndim, do_feedback=False)
     nblocks_total = (n // nb) ** ndim
@@ -244,17 +250,20 @@ def test_nccl_ranks_equal_one_rank(world):
         r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
         parts = [pickle.load(open(os.path.join(d, f"rank{q}.pkl"), "rb")) for q in range(world)]
+    assert all(p.pop("exchange_mode") == (2 if p2p == "1" else 1) for p in parts), "the requested exchange path did not run"
     _compare(one, parts, cycles)
 
 
+@pytest.mark.parametrize("p2p", ["1", "0"])
 @pytest.mark.parametrize("world", [2, 4])
-def test_nccl_ddmc_ranks_equal_one_rank(world):
+def test_nccl_ddmc_ranks_equal_one_rank(world, p2p, monkeypatch):
     """stepdiff_smr_ddmc over NCCL: the density / sie ghost exchange and the photon exchange both
-    run inside jb_radiation_step."""
+    run inside jb_radiation_step (photon exchange by direct peer stores when JB_P2P=1)."""
     import torch
     from jaybenne_b200 import Mcblock, device_api
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
+    monkeypatch.setenv("JB_P2P", p2p)
     deck, ov, cycles = "stepdiff_smr_ddmc", [("jaybenne", "num_particles", 50000)], 2
     one_mb = Mcblock(pu.make_pin(deck, overrides=ov, ci=True), api=device_api())
     one_mb.ProblemGenerator()
@@ -272,4 +281,5 @@ def test_nccl_ddmc_ranks_equal_one_rank(world):
         r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
         parts = [pickle.load(open(os.path.join(d, f"rank{q}.pkl"), "rb")) for q in range(world)]
+    assert all(p.pop("exchange_mode") == (2 if p2p == "1" else 1) for p in parts), "the requested exchange path did not run"
     _compare(one, parts, cycles, extra_counts=("n_ddmc_segments",))

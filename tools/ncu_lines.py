@@ -44,6 +44,7 @@ def sass_lines(section_pat):
 def main():
     rep, pat = sys.argv[1], sys.argv[2]
     top = int(sys.argv[3]) if len(sys.argv) > 3 else 60
+    by_samples = len(sys.argv) > 4 and sys.argv[4] == "samples"   # rank the lines by stall samples instead
     lines = sass_lines(pat)
     raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
@@ -67,7 +68,7 @@ def main():
     print(f"total warp-inst {tot[0]:.4g}  thread-inst {tot[1]:.4g}  avg active {tot[1] / max(tot[0], 1):.2f}  samples {tot[2]}")
     print("\nby source line (share of warp instructions, of thread instructions, avg active lanes, share of stall samples)")
     src_cache = {}
-    for loc, a in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+    for loc, a in sorted(agg.items(), key=lambda kv: -kv[1][2 if by_samples else 0])[:top]:
         f = loc[0]
         if f not in src_cache:
             cand = glob.glob(os.path.join(ROOT, "jaybenne_b200", "csrc", "**", f), recursive=True)
