@@ -76,6 +76,37 @@ struct Rng {
   }
 };
 
+// The ten round keys of one Philox key pair, computed once on the host (k[2r] = key0 + r * 0x9E3779B9,
+// k[2r+1] = key1 + r * 0xBB67AE85). A kernel that holds them in its parameter block reads each one as a
+// constant-bank operand of the round's XOR; bumping the keys in the loop cost two uniform adds per round, a third
+// of the generator's instructions (profiles/r02_v11_*.md).
+struct PKeys {
+  uint32_t k[20];
+};
+__host__ __device__ inline PKeys make_pkeys(uint32_t k0, uint32_t k1) {
+  PKeys K;
+  for (int r = 0; r < 10; ++r) {
+    K.k[2 * r] = k0 + (uint32_t)r * 0x9E3779B9u;
+    K.k[2 * r + 1] = k1 + (uint32_t)r * 0xBB67AE85u;
+  }
+  return K;
+}
+__device__ __forceinline__ void philox_pair(uint32_t blk, uint32_t id0, uint32_t id1, uint32_t id2, const PKeys &K,
+                                            double &d0, double &d1) {
+  uint32_t c0 = blk, c1 = id0, c2 = id1, c3 = id2;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    c0 = hi1 ^ c1 ^ K.k[2 * r];
+    c1 = lo1;
+    c2 = hi0 ^ c3 ^ K.k[2 * r + 1];
+    c3 = lo0;
+  }
+  d0 = (double)((((uint64_t)c1 << 32) | c0) >> 11) * 1.1102230246251565e-16;
+  d1 = (double)((((uint64_t)c3 << 32) | c2) >> 11) * 1.1102230246251565e-16;
+}
+
 // doubles #2*blk and #2*blk+1 of a stream in one straight-line Philox evaluation (what two
 // consecutive Rng::drand() calls starting at an even draw counter return)
 __device__ __forceinline__ void philox_pair(uint32_t blk, uint32_t id0, uint32_t id1, uint32_t id2, uint32_t k0,

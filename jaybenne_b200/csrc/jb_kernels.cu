@@ -421,11 +421,11 @@ __global__ void __launch_bounds__(256, 4) k_source_emit(StepParams P, int first_
       // phi xi0 | xi1 xi2 | xi3 xi4 | t — one Philox block per pair, straight-line (same values as Rng::drand)
       const uint32_t id0 = (uint32_t)np, id1 = (uint32_t)b.gid;
       double d0, d1, d2, d3, d4, d5, d6, d7, d8, d9;
-      philox_pair(0u, id0, id1, call, P.key0, P.key1_particle, d0, d1);
-      philox_pair(1u, id0, id1, call, P.key0, P.key1_particle, d2, d3);
-      philox_pair(2u, id0, id1, call, P.key0, P.key1_particle, d4, d5);
-      philox_pair(3u, id0, id1, call, P.key0, P.key1_particle, d6, d7);
-      philox_pair(4u, id0, id1, call, P.key0, P.key1_particle, d8, d9);
+      philox_pair(0u, id0, id1, call, P.rk, d0, d1);
+      philox_pair(1u, id0, id1, call, P.rk, d2, d3);
+      philox_pair(2u, id0, id1, call, P.rk, d4, d5);
+      philox_pair(3u, id0, id1, call, P.rk, d6, d7);
+      philox_pair(4u, id0, id1, call, P.rk, d8, d9);
       const double x = xi + b.dx[0] * (d0 - 0.5);
       const double y = yi + b.dx[1] * (d1 - 0.5);
       const double z = zi + b.dx[2] * (d2 - 0.5);
@@ -439,7 +439,7 @@ __global__ void __launch_bounds__(256, 4) k_source_emit(StepParams P, int first_
       uint32_t ndraws = 10u;
       if (source_type == JB_SOURCE_EMISSION) {
         double d10, d11;
-        philox_pair(5u, id0, id1, call, P.key0, P.key1_particle, d10, d11);
+        philox_pair(5u, id0, id1, call, P.rk, d10, d11);
         tp = t_start + d10 * dt;
         ndraws = 11u;
       }

@@ -151,6 +151,7 @@ struct StepParams {
   unsigned long long *work;  // chunk counter of the persistent transport kernel (zero at launch)
   const long long *range;    // non-null: the kernel reads (first, n) here (P2PState::range) instead of its arguments
   uint32_t key0, key1_particle, key1_cell;
+  PKeys rk;  // the ten Philox round keys of the particle stream (key0, key1_particle bumped per round)
   int use_ddmc;
   double tau_ddmc;
 };

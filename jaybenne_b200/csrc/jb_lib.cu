@@ -245,6 +245,7 @@ static StepParams make_params(jb_ctx *c) {
   P.key0 = (uint32_t)((uint64_t)c->cfg.seed);
   P.key1_particle = (uint32_t)((uint64_t)c->cfg.seed >> 32) ^ STREAM_PARTICLE;
   P.key1_cell = (uint32_t)((uint64_t)c->cfg.seed >> 32) ^ STREAM_CELL;
+  P.rk = make_pkeys(P.key0, P.key1_particle);
   P.use_ddmc = c->cfg.use_ddmc;
   P.tau_ddmc = c->cfg.tau_ddmc;
   return P;

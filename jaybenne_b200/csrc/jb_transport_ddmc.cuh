@@ -23,13 +23,13 @@
 // replaces the per-draw cache test of Rng (half the lanes of every call site re-evaluating a block:
 // profiles/r01_v4_ncu_transport_ddmc_cells64.md, Philox lines at 17 of 32 lanes). Same streams, same
 // draw order, same arithmetic as ddmc_albedo / ddmc_step / face_iso_dir in jb_device.cuh.
-__device__ __forceinline__ double rng2_draw1(Rng2 &r, uint32_t k0, uint32_t k1) {
+__device__ __forceinline__ double rng2_draw1(Rng2 &r, const PKeys &K) {
   double v;
   if (r.n & 1u) {
     v = Rng2::to_double(r.clo, r.chi);  // the carried half of block n >> 1
   } else {
     uint32_t w0, w1, w2, w3;
-    r.block(r.n >> 1, k0, k1, w0, w1, w2, w3);
+    r.block(r.n >> 1, K, w0, w1, w2, w3);
     v = Rng2::to_double(w0, w1);
     r.clo = w2;
     r.chi = w3;
@@ -49,7 +49,7 @@ __device__ __forceinline__ void face_iso_dir2(const double vv, const double xi_m
   v3 = vv * nu * sn;
 }
 template <int NDIM>
-__device__ __forceinline__ void ddmc_albedo2(Rng2 &rng, const uint32_t k0, const uint32_t k1, const CellEnv &c,
+__device__ __forceinline__ void ddmc_albedo2(Rng2 &rng, const PKeys &K, const CellEnv &c,
                                              const double vv, Photon &p, bool &is_rejected) {
   constexpr bool multi_d = NDIM >= 2, three_d = NDIM == 3;
   const double dx = c.xu - c.xl, dy = c.yu - c.yl, dz = c.zu - c.zl;
@@ -68,9 +68,9 @@ __device__ __forceinline__ void ddmc_albedo2(Rng2 &rng, const uint32_t k0, const
     const double sign_in = upper ? -1.0 : 1.0;
     const double Pf = jbm::div_normal(2.0 / 3.0, (c.aa + c.ss) * dcell + 2.0 * LAM_EXT);  // denominator >= 1.42
     const double P = 2.0 * Pf * (1.0 + jbm::div_normal(sign_in * 1.5 * vn, vv));
-    if (rng2_draw1(rng, k0, k1) > P) {
+    if (rng2_draw1(rng, K) > P) {
       double xi_mu, xi_phi, v1, v2, v3;
-      rng.draw2(k0, k1, xi_mu, xi_phi);
+      rng.draw2(K, xi_mu, xi_phi);
       face_iso_dir2(upper ? vv : -vv, xi_mu, xi_phi, v1, v2, v3);
       unpermute_dir(axis, v1, v2, v3, p.vx, p.vy, p.vz);
       const double lo = axis == 0 ? c.xl : (axis == 1 ? c.yl : c.zl);
@@ -92,7 +92,7 @@ __device__ __forceinline__ void ddmc_albedo2(Rng2 &rng, const uint32_t k0, const
 // re-derive the cell index the way the reference does (Xtoijk); in every other outcome ip / jp / kp are
 // already what Xtoijk returns (cell centre, or DDMC-offset beyond a face with the index moved).
 template <int NDIM>
-__device__ __forceinline__ void ddmc_step2(Rng2 &rng, const uint32_t k0, const uint32_t k1, const double t_end,
+__device__ __forceinline__ void ddmc_step2(Rng2 &rng, const PKeys &K, const double t_end,
                                            const CellEnv &c, const double vv, const double P[6], Photon &p,
                                            bool &is_absorbed, bool &resampled) {
   constexpr int multi_d = NDIM >= 2 ? 1 : 0, three_d = NDIM == 3 ? 1 : 0;
@@ -110,7 +110,7 @@ __device__ __forceinline__ void ddmc_step2(Rng2 &rng, const uint32_t k0, const u
   const double leak_tot = th4 + leakz_u;
   const double cdf_ddmc = c.ff * c.aa + leak_tot + rmin;
   double xi_dt, xi_b;  // the second draw is xi of an event or z of the census resampling
-  rng.draw2(k0, k1, xi_dt, xi_b);
+  rng.draw2(K, xi_dt, xi_b);
   const double dt_ddmc = -jbm::log_unit(xi_dt) / (vv * cdf_ddmc);
   const double dt_end = t_end - p.t;
   const bool is_ddmc_event = dt_ddmc < dt_end;
@@ -137,7 +137,7 @@ __device__ __forceinline__ void ddmc_step2(Rng2 &rng, const uint32_t k0, const u
         p.y = axis == 1 ? fy : c.yl + 0.5 * dy;
         p.z = axis == 2 ? fz : c.zl + 0.5 * dz;
         double xi_mu, xi_phi, v1, v2, v3;
-        rng.draw2(k0, k1, xi_mu, xi_phi);
+        rng.draw2(K, xi_mu, xi_phi);
         face_iso_dir2(upper ? vv : -vv, xi_mu, xi_phi, v1, v2, v3);
         unpermute_dir(axis, v1, v2, v3, p.vx, p.vy, p.vz);
       }
@@ -145,8 +145,8 @@ __device__ __forceinline__ void ddmc_step2(Rng2 &rng, const uint32_t k0, const u
   } else {
     resampled = true;
     double xi_x, xi_y, xi_mu, xi_phi;
-    rng.draw2(k0, k1, xi_x, xi_y);
-    rng.draw2(k0, k1, xi_mu, xi_phi);
+    rng.draw2(K, xi_x, xi_y);
+    rng.draw2(K, xi_mu, xi_phi);
     p.z = c.zl + xi_b * dz;
     p.x = c.xl + xi_x * dx;
     p.y = c.yl + xi_y * dy;
@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
   p.ip = p.jp = p.kp = 0;
   q.f = q.hnu = q.bpref = 0.0;
   rng.id0 = rng.id1 = rng.id2 = rng.n = rng.clo = rng.chi = 0u;
-  const uint32_t k0 = P.key0, k1 = P.key1_particle;
+  const PKeys &K = P.rk;
 
   unsigned c_seg = 0, c_ddmc = 0, c_scat = 0;
   // energies stay per lane and are folded by a shuffle tree at the end: stiff problems absorb ~all of
@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
             p.x = l_x; p.y = l_y; p.z = l_z;
             p.vx = l_vx; p.vy = l_vy; p.vz = l_vz;
             q = photon_freq(P.cl, l_e);
-            rng.load(ia.x, ia.y, ib.x, ib.y, k0, k1);
+            rng.load(ia.x, ia.y, ib.x, ib.y, K);
             gid = m.local_gid[lc.x];
             BlkReg B;
             load_block(m, gid, B);
@@ -289,13 +289,13 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
           Pf[2] = 0.0; Pf[5] = 0.0;
         }
         bool resampled = false;
-        ddmc_albedo2<NDIM>(rng, k0, k1, c, vv, p, is_rejected);
-        if (!is_rejected) ddmc_step2<NDIM>(rng, k0, k1, t_end, c, vv, Pf, p, is_absorbed, resampled);
+        ddmc_albedo2<NDIM>(rng, K, c, vv, p, is_rejected);
+        if (!is_rejected) ddmc_step2<NDIM>(rng, K, t_end, c, vv, Pf, p, is_absorbed, resampled);
         // Xtoijk (transport_ddmc.cpp:198) only where the position was drawn or pushed back out of the cell
         if (is_rejected || resampled) xtoijk<NDIM>(B, p, p.ip, p.jp, p.kp);
       } else {
         double xi_abs, xi_sc;
-        rng.draw2(k0, k1, xi_abs, xi_sc);
+        rng.draw2(K, xi_abs, xi_sc);
         int di, dj, dk;
         unsigned bad_div = 0;
         imc_step_lockstep<NDIM>(xi_abs, xi_sc, t_end, c, vv, B.dx_push, p, is_absorbed, is_scattered, di, dj, dk, bad_div);
@@ -348,9 +348,9 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
               load_block(m, gid, NB);
               xtoijk<NDIM>(NB, p, p.ip, p.jp, p.kp);
               Rng g;  // the block-face sampler (rare) runs on the per-draw generator, same stream
-              g.init(rng.id0, rng.id1, rng.id2, rng.n, k0, k1);
+              g.init(rng.id0, rng.id1, rng.id2, rng.n, P.key0, P.key1_particle);
               bface_sample<NDIM>(P, NB, p, g);
-              if (g.n != rng.n) rng.load(rng.id0, rng.id1, rng.id2, g.n, k0, k1);
+              if (g.n != rng.n) rng.load(rng.id0, rng.id1, rng.id2, g.n, K);
             }
           }
         }
@@ -368,7 +368,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
       } else {
         if (is_scattered) {
           double xi_mu, xi_phi;
-          rng.draw2(k0, k1, xi_mu, xi_phi);
+          rng.draw2(K, xi_mu, xi_phi);
           scatter_iso2(xi_mu, xi_phi, vv, p.vx, p.vy, p.vz);
           c_scat++;
           kind |= JB_EV_SCATTER;

@@ -44,27 +44,25 @@ __device__ __forceinline__ CellProps load_props(const CellProps *p) {
 struct Rng2 {
   uint32_t id0, id1, id2, n, clo, chi;
 
-  __device__ __forceinline__ void block(uint32_t blk, uint32_t k0, uint32_t k1, uint32_t &w0, uint32_t &w1,
+  __device__ __forceinline__ void block(uint32_t blk, const PKeys &K, uint32_t &w0, uint32_t &w1,
                                         uint32_t &w2, uint32_t &w3) const {
-    uint32_t c0 = blk, c1 = id0, c2 = id1, c3 = id2, a = k0, b = k1;
+    uint32_t c0 = blk, c1 = id0, c2 = id1, c3 = id2;
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
       const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
       const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-      c0 = hi1 ^ c1 ^ a;
+      c0 = hi1 ^ c1 ^ K.k[2 * r];  // round keys straight from the kernel-parameter bank (PKeys)
       c1 = lo1;
-      c2 = hi0 ^ c3 ^ b;
+      c2 = hi0 ^ c3 ^ K.k[2 * r + 1];
       c3 = lo0;
-      a += 0x9E3779B9u;
-      b += 0xBB67AE85u;
     }
     w0 = c0; w1 = c1; w2 = c2; w3 = c3;
   }
-  __device__ __forceinline__ void load(uint32_t a, uint32_t b, uint32_t c, uint32_t draws, uint32_t k0, uint32_t k1) {
+  __device__ __forceinline__ void load(uint32_t a, uint32_t b, uint32_t c, uint32_t draws, const PKeys &K) {
     id0 = a; id1 = b; id2 = c; n = draws; clo = chi = 0u;
     if (draws & 1u) {
       uint32_t w0, w1;
-      block(draws >> 1, k0, k1, w0, w1, clo, chi);
+      block(draws >> 1, K, w0, w1, clo, chi);
     }
   }
   static __device__ __forceinline__ double to_double(uint32_t lo, uint32_t hi) {
@@ -72,9 +70,9 @@ struct Rng2 {
     return (double)(u >> 11) * 1.1102230246251565e-16;
   }
   // draws #n and #n+1
-  __device__ __forceinline__ void draw2(uint32_t k0, uint32_t k1, double &a, double &b) {
+  __device__ __forceinline__ void draw2(const PKeys &K, double &a, double &b) {
     uint32_t w0, w1, w2, w3;
-    block((n + 1u) >> 1, k0, k1, w0, w1, w2, w3);
+    block((n + 1u) >> 1, K, w0, w1, w2, w3);
     const bool odd = (n & 1u) != 0;
     a = to_double(odd ? clo : w0, odd ? chi : w1);
     b = to_double(odd ? w0 : w2, odd ? w1 : w3);
@@ -326,7 +324,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
     // reference's, applied before the photon's next segment instead of right after the last one.
     if (have && (pend_scat || need_carry)) {
       uint32_t w0, w1, w2, w3;
-      rng.block(pend_scat ? (rng.n + 1u) >> 1 : rng.n >> 1, P.key0, P.key1_particle, w0, w1, w2, w3);
+      rng.block(pend_scat ? (rng.n + 1u) >> 1 : rng.n >> 1, P.rk, w0, w1, w2, w3);
       if (pend_scat) {
         const bool odd = (rng.n & 1u) != 0;
         const double xi_mu = Rng2::to_double(odd ? rng.clo : w0, odd ? rng.chi : w1);
@@ -352,7 +350,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
       const double2 gx = __ldg(&geo->xd[0]), gy = __ldg(&geo->xd[1]), gz = __ldg(&geo->xd[2]);
       const double dx_cell = __ldg(&geo->dx_push);
       double xi_abs, xi_sc;
-      rng.draw2(P.key0, P.key1_particle, xi_abs, xi_sc);
+      rng.draw2(P.rk, xi_abs, xi_sc);
       CellEnv c;
       {
         // coords.Xc<d>(i) -/+ dx/2 (transport.cpp:114-119), Xc as UniformCartesian computes it
@@ -467,7 +465,7 @@ __global__ void __launch_bounds__(IMC_TPB, MINB)
           pend_scat = true;  // new direction from the shared extra block at the top of the next iteration
         } else {             // scattered exactly into census (rounding): finish it here, the lane is freed below
           double xi_mu, xi_phi;
-          rng.draw2(P.key0, P.key1_particle, xi_mu, xi_phi);
+          rng.draw2(P.rk, xi_mu, xi_phi);
           scatter_iso2(xi_mu, xi_phi, vv, p.vx, p.vy, p.vz);
           c_scat++;
         }

@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
             Rng2 g;
             g.id0 = ia.x; g.id1 = ia.y; g.id2 = ib.x;
             uint32_t w0_, w1_;
-            g.block(ib.y >> 1, P.key0, P.key1_particle, w0_, w1_, cy.x, cy.y);
+            g.block(ib.y >> 1, P.rk, w0_, w1_, cy.x, cy.y);
           }
           W.carry[s] = cy;
           const int gid = m.local_gid[lc.x];
@@ -249,7 +249,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
         const uint2 ia = W.ida[s], ib = W.idb[s], cy = W.carry[s];
         rng.id0 = ia.x; rng.id1 = ia.y; rng.id2 = ib.x; rng.n = ib.y; rng.clo = cy.x; rng.chi = cy.y;
         double xi_mu, xi_phi, vx, vy, vz;
-        rng.draw2(P.key0, P.key1_particle, xi_mu, xi_phi);
+        rng.draw2(P.rk, xi_mu, xi_phi);
         scatter_iso2(xi_mu, xi_phi, vv, vx, vy, vz);
         W.vx[s] = vx; W.vy[s] = vy; W.vz[s] = vz;
         W.idb[s].y = rng.n;
@@ -287,7 +287,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
       p.x = W.x[s]; p.y = W.y[s]; p.z = W.z[s]; p.t = W.t[s];
       p.vx = W.vx[s]; p.vy = W.vy[s]; p.vz = W.vz[s];
       double xi_abs, xi_sc;
-      rng.draw2(P.key0, P.key1_particle, xi_abs, xi_sc);
+      rng.draw2(P.rk, xi_abs, xi_sc);
       CellEnv c;
       {
         // coords.Xc<d>(i) -/+ dx/2 (transport.cpp:114-119), Xc as UniformCartesian computes it
@@ -408,7 +408,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
           newst = PS_PEND;  // new direction in the scatter phase
         } else {            // scattered exactly into census (rounding): finish it here
           double xi_mu, xi_phi;
-          rng.draw2(P.key0, P.key1_particle, xi_mu, xi_phi);
+          rng.draw2(P.rk, xi_mu, xi_phi);
           scatter_iso2(xi_mu, xi_phi, vv, p.vx, p.vy, p.vz);
           W.vx[s] = p.vx; W.vy[s] = p.vy; W.vz[s] = p.vz;
           c_scat++;
