@@ -428,6 +428,21 @@ def main():
     value = seg_all / (ms_max * 1e-3)
     steps_identical = all(st["n_segments"] == sts[0]["n_segments"] and st["n_end"] == sts[0]["n_end"] for st in sts)
     inv = W.invariants(last)
+    # device-timed phases of the last step (jb_step_timeline): where a rank's step goes, and how far the ranks differ
+    tl = jb.step_timeline()
+    phases = {}
+    for name, tms in tl:
+        phases.setdefault(name, []).append(round(tms, 3))
+    tl_sum = {k: sum(v) for k, v in phases.items()}
+    tl_keys = ("fields", "source", "transport", "exchange", "stats", "squeeze", "tally", "end")
+    tl_max = reduce([tl_sum.get(k, 0.0) for k in tl_keys], "max")
+    tl_min = [-v for v in reduce([-tl_sum.get(k, 0.0) for k in tl_keys], "max")]
+    timeline = {"rank0_ms": phases, "sum_ms_max_over_ranks": dict(zip(tl_keys, (round(v, 3) for v in tl_max))),
+                "sum_ms_min_over_ranks": dict(zip(tl_keys, (round(v, 3) for v in tl_min))),
+                "exchange_mode": {0: "none (one rank)", 1: "nccl send/recv per iteration", 2: "direct peer stores over NVLink"}.get(
+                    jb.exchange_mode(), "?"),
+                "note": "last timed step; a multi-rank step has one transport + exchange pair per iteration, and the exchange "
+                        "phase includes waiting for the slowest peer"}
 
     # ---- timed: end to end through the C ABI with host buffers
     e2e = None
@@ -579,7 +594,7 @@ def main():
                 "invariants": dict(inv, steps_identical=steps_identical,
                                    note="all-reduced over the ranks; every step sources the same photons (jb_reset_streams), "
                                         "so these are equal for every N, K and W"),
-                "variants": variants or None, "continuing": continuing,
+                "timeline": timeline, "variants": variants or None, "continuing": continuing,
                 "last_step_rank0": {k: last[k] for k in ("n_start", "n_sourced", "n_absorbed", "n_end", "n_sent", "n_received",
                                                           "n_segments", "n_scatters", "n_block_crossings", "n_iterations")}}
         print(json.dumps(line))

@@ -264,6 +264,23 @@ jb_status jb_reset_streams(jb_ctx *ctx);
  * 1 = count all-gather + grouped ncclSend / ncclRecv per iteration, 2 = direct stores into the peers'
  * IPC-mapped inboxes over NVLink with the loop state on the device (needs jb_set_capacity; JB_P2P=0 disables) */
 int32_t jb_exchange_mode(const jb_ctx *ctx);
+/* Device-timed phases of the last jb_radiation_step, in stream order (CUDA events on the context's stream; no
+ * reference counterpart — the reference's timing is Kokkos profiling regions, jaybenne.cpp:87,115,127,145).
+ * Entry q: the phase labels[q] (JB_TL_*) took ms[q] milliseconds; *n = number of phases (may exceed cap). A
+ * multi-rank step has one JB_TL_TRANSPORT + JB_TL_EXCHANGE pair per transport iteration; the exchange phase
+ * includes the time this rank waited for its peers. */
+enum {
+  JB_TL_BEGIN = 0,      /* (never reported: opens the first phase) */
+  JB_TL_FIELDS = 1,     /* census at cycle start, Fleck factor, DDMC face probabilities, packed cell records */
+  JB_TL_SOURCE = 2,     /* SourcePhotons (emission) */
+  JB_TL_TRANSPORT = 3,  /* one launch of the transport kernel */
+  JB_TL_EXCHANGE = 4,   /* swarm exchange of one iteration: counts, send / receive or peer stores, unpack */
+  JB_TL_STATS = 5,      /* counters and energy sums folded and read back */
+  JB_TL_SQUEEZE = 6,    /* pool squeeze (only when occupancy dropped below the floor) */
+  JB_TL_TALLY = 7,      /* EvaluateRadiationEnergy */
+  JB_TL_END = 8         /* UpdateFluid (+ cell sort when sort_interval asks for it) */
+};
+jb_status jb_step_timeline(const jb_ctx *ctx, int32_t *labels, float *ms, int32_t cap, int32_t *n);
 /* change jb_config::sort_interval of a live context (0 = never sort the pool by (meshblock, cell)) */
 jb_status jb_set_sort_interval(jb_ctx *ctx, int32_t every_n_cycles);
 /* cumulative stats since the last jb_radiation_step / jb_stats_begin began */

@@ -1179,6 +1179,83 @@ void launch_compact(const StepParams &P, long long n, long long n_alive, long lo
 }
 
 // ---------------------------------------------------------------------------------------
+// Order-preserving squeeze: the live photons keep their relative order (so a pool laid down cell by cell stays
+// near-sorted, see jb_transport_pool.cuh v12). Three steps on 1024-slot chunks: (1) one pass over `loc` writes a
+// live-bit word per 32 slots and a count per chunk; (2) exclusive scan of the counts; (3) every swarm array is
+// streamed through the one scratch array — a lane whose bit is set copies its element to chunk offset + rank —
+// and swaps storage with it. The passes read 1 bit per slot instead of `loc`, and the sectors of a chunk's
+// hole-only tail are never touched: traffic ~ 16 B per live photon and array.
+// ---------------------------------------------------------------------------------------
+static constexpr int SQ_CHUNK = 1024;  // 32 mask words; one CTA of 256 threads, 4 rounds
+__global__ void __launch_bounds__(256) k_squeeze_flags(const int2 *__restrict__ loc, long long n, unsigned *__restrict__ mask,
+                                                       int *__restrict__ cnt) {
+  __shared__ int part[8];
+  const long long base = blockIdx.x * (long long)SQ_CHUNK;
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  int2 lc[4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const long long idx = base + r * 256 + threadIdx.x;
+    lc[r] = idx < n ? __ldcs(&loc[idx]) : make_int2(-1, 0);
+  }
+  int a = 0;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const unsigned mk = __ballot_sync(0xffffffffu, lc[r].x >= 0);
+    if (lane == 0) mask[blockIdx.x * 32ll + r * 8 + warp] = mk;
+    a += __popc(mk);
+  }
+  if (lane == 0) part[warp] = a;
+  __syncthreads();
+  if (threadIdx.x == 0) cnt[blockIdx.x] = part[0] + part[1] + part[2] + part[3] + part[4] + part[5] + part[6] + part[7];
+}
+__global__ void __launch_bounds__(256) k_squeeze_move(const unsigned long long *__restrict__ src,
+                                                      unsigned long long *__restrict__ dst,
+                                                      const unsigned *__restrict__ mask,
+                                                      const long long *__restrict__ prefix) {
+  __shared__ unsigned mk[32];
+  __shared__ int off[32];
+  const long long base = blockIdx.x * (long long)SQ_CHUNK;
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  if (threadIdx.x < 32) {
+    const unsigned w = mask[blockIdx.x * 32ll + threadIdx.x];
+    mk[threadIdx.x] = w;
+    // exclusive scan of the 32 word counts (word = round * 8 + warp = slot order)
+    int c = __popc(w), inc = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int up = __shfl_up_sync(0xffffffffu, inc, o);
+      if ((int)lane >= o) inc += up;
+    }
+    off[threadIdx.x] = inc - c;
+  }
+  __syncthreads();
+  const long long out = prefix[blockIdx.x];
+  unsigned long long v[4];
+  bool live[4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    live[r] = (mk[r * 8 + warp] >> lane) & 1u;
+    if (live[r]) v[r] = __ldcs(&src[base + r * 256 + threadIdx.x]);
+  }
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+    if (live[r]) dst[out + off[r * 8 + warp] + __popc(mk[r * 8 + warp] & ((1u << lane) - 1u))] = v[r];
+}
+// `loc` of the n slots is the still-unsqueezed array; returns nothing the host needs (live count is known)
+void launch_squeeze_flags(const int2 *loc, long long n, unsigned *mask, int *cnt, cudaStream_t st) {
+  const long long nchunk = (n + SQ_CHUNK - 1) / SQ_CHUNK;
+  if (nchunk > 0) k_squeeze_flags<<<(unsigned)nchunk, 256, 0, st>>>(loc, n, mask, cnt);
+}
+void launch_squeeze_move(const void *src, void *dst, long long n, const unsigned *mask, const long long *prefix,
+                         cudaStream_t st) {
+  const long long nchunk = (n + SQ_CHUNK - 1) / SQ_CHUNK;
+  if (nchunk > 0)
+    k_squeeze_move<<<(unsigned)nchunk, 256, 0, st>>>((const unsigned long long *)src, (unsigned long long *)dst, mask, prefix);
+}
+long long squeeze_chunks(long long n) { return (n + SQ_CHUNK - 1) / SQ_CHUNK; }
+
+// ---------------------------------------------------------------------------------------
 // Receive side of the swarm exchange: append records to the pool (Swarm::Receive).
 // ---------------------------------------------------------------------------------------
 __device__ __forceinline__ void unpack_records(const StepParams &P, const ExRecord *rec, long long nrec, long long slot0,

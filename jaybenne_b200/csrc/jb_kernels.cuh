@@ -202,6 +202,10 @@ void launch_p2p_push(const StepParams &P, P2PState *state, const P2PPeers *peers
 void launch_p2p_wait_unpack(const StepParams &P, P2PState *state, P2PMail *my_mail, ExRecord *inbox0, ExRecord *inbox1,
                             int n_ranks, long long inbox_cap, double t_end, bool ddmc, cudaStream_t st);
 // cell sort: key = blk * ncell + cell
+void launch_squeeze_flags(const int2 *loc, long long n, unsigned *mask, int *cnt, cudaStream_t st);
+void launch_squeeze_move(const void *src, void *dst, long long n, const unsigned *mask, const long long *prefix,
+                         cudaStream_t st);
+long long squeeze_chunks(long long n);
 void launch_sort_keys(const StepParams &P, long long n, int *cell_count, cudaStream_t st);
 void launch_sort_perm(const StepParams &P, long long n, long long *cell_offset, unsigned int *perm, cudaStream_t st);
 void launch_selftest_division(long long n, unsigned long long *mismatches, cudaStream_t st);

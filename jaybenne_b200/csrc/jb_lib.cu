@@ -88,6 +88,12 @@ struct jb_ctx {
   // scratch
   double *d_tmp = nullptr;            // one SoA-array-sized scratch: rotates with the arrays in the cell sort
   unsigned int *d_perm = nullptr;     // sort permutation
+  // order-preserving squeeze (k_squeeze_*): live bits, per-chunk counts / offsets, scan scratch
+  unsigned *d_sq_mask = nullptr;
+  int *d_sq_cnt = nullptr;
+  long long *d_sq_prefix = nullptr, *d_sq_scan = nullptr;
+  long long sq_chunks_cap = 0;
+  int squeeze_mode = -1;              // 1 order-preserving (default), 0 tail photons into holes (JB_SQUEEZE=tail)
   int *d_cnt = nullptr;               // per-cell counts
   long long *d_prefix = nullptr;      // per-cell offsets
   long long *d_scan = nullptr, *d_total = nullptr;
@@ -123,6 +129,12 @@ struct jb_ctx {
   P2PPeers *d_peers = nullptr;
   std::vector<void *> ipc_opened;      // peer mappings to close
   cudaEvent_t it_ev[2 * 16] = {};      // transport launch brackets of the queued iterations
+  // phase marks of the last jb_radiation_step (jb_step_timeline): event i closes the phase labelled tl_label[i]
+  static constexpr int TL_CAP = 96;
+  cudaEvent_t tl_ev[TL_CAP] = {};
+  int tl_label[TL_CAP] = {};
+  float tl_ms[TL_CAP] = {};
+  int tl_n = 0, tl_done = 0;
   // event log
   jb_event *d_events = nullptr;
   long long event_cap = 0;
@@ -258,11 +270,33 @@ static void swarm_arrays(Swarm &s, void **out[12]) {
   out[8] = (void **)&s.vz; out[9] = (void **)&s.loc; out[10] = (void **)&s.ida; out[11] = (void **)&s.idb;
 }
 
+// jb_step_timeline: a mark closes the phase `label` (JB_TL_*) on the stream; durations are read after the step
+static void tl_mark(jb_ctx *c, int label) {
+  if (c->tl_n >= jb_ctx::TL_CAP) return;
+  cudaEvent_t &e = c->tl_ev[c->tl_n];
+  if (!e && cudaEventCreate(&e) != cudaSuccess) return;
+  cudaEventRecord(e, c->stream);
+  c->tl_label[c->tl_n++] = label;
+}
+static void tl_finish(jb_ctx *c) {  // after the stream has been synchronised
+  c->tl_done = 0;
+  for (int q = 1; q < c->tl_n; ++q) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->tl_ev[q - 1], c->tl_ev[q]) != cudaSuccess) ms = -1.f;
+    c->tl_label[c->tl_done] = c->tl_label[q];
+    c->tl_ms[c->tl_done++] = ms;
+  }
+  cudaGetLastError();
+}
+
 static void free_swarm(jb_ctx *c) {
   void **arr[12];
   swarm_arrays(c->s, arr);
   for (auto a : arr) dfree(*a);
   dfree(c->d_tmp); dfree(c->d_perm);
+  dfree(c->d_sq_mask); dfree(c->d_sq_cnt); dfree(c->d_sq_prefix); dfree(c->d_sq_scan);
+  c->d_sq_mask = nullptr; c->d_sq_cnt = nullptr; c->d_sq_prefix = c->d_sq_scan = nullptr;
+  c->sq_chunks_cap = 0;
   dfree(c->out.rec); dfree(c->out.count); dfree(c->d_inbox);
   memset(&c->s, 0, sizeof(c->s));
   memset(&c->out, 0, sizeof(c->out));
@@ -395,6 +429,8 @@ void jb_destroy(jb_ctx *c) {
   for (void *q : c->ipc_opened) cudaIpcCloseMemHandle(q);
   dfree(c->d_mail); dfree(c->d_p2p_inbox[0]); dfree(c->d_p2p_inbox[1]); dfree(c->d_p2p_state); dfree(c->d_peers);
   if (c->h_p2p_state) cudaFreeHost(c->h_p2p_state);
+  for (auto &e : c->tl_ev)
+    if (e) cudaEventDestroy(e);
   for (auto &e : c->it_ev)
     if (e) cudaEventDestroy(e);
   if (c->comm && nccl_api().ok) nccl_api().CommDestroy(c->comm);
@@ -743,6 +779,47 @@ static jb_status compact(jb_ctx *c, long long n_dead, bool force = false) {
     c->n = 0;
     return JB_OK;
   }
+  if (c->squeeze_mode < 0) {
+    const char *v = getenv("JB_SQUEEZE");
+    c->squeeze_mode = (v && strcmp(v, "tail") == 0) ? 0 : 1;
+  }
+  if (c->squeeze_mode == 1) {
+    // order-preserving: every array streams through the scratch array and swaps storage with it. Falls back to
+    // the in-place tail-into-holes squeeze when the scratch array cannot be allocated.
+    const long long nchunk = squeeze_chunks(c->n);
+    bool ok = true;
+    if (!c->d_tmp) ok = dalloc(&c->d_tmp, c->capacity) == cudaSuccess;
+    if (ok && nchunk > c->sq_chunks_cap) {
+      dfree(c->d_sq_mask); dfree(c->d_sq_cnt); dfree(c->d_sq_prefix); dfree(c->d_sq_scan);
+      c->d_sq_mask = nullptr; c->d_sq_cnt = nullptr; c->d_sq_prefix = c->d_sq_scan = nullptr;
+      c->sq_chunks_cap = squeeze_chunks(c->capacity) + 1;
+      ok = dalloc(&c->d_sq_mask, c->sq_chunks_cap * 32) == cudaSuccess && dalloc(&c->d_sq_cnt, c->sq_chunks_cap) == cudaSuccess &&
+           dalloc(&c->d_sq_prefix, c->sq_chunks_cap + 1) == cudaSuccess &&
+           dalloc(&c->d_sq_scan, scan_scratch_elems(c->sq_chunks_cap)) == cudaSuccess;
+      if (!ok) c->sq_chunks_cap = 0;
+    }
+    if (ok) {
+      cudaStream_t st = c->stream;
+      launch_squeeze_flags(c->s.loc, c->n, c->d_sq_mask, c->d_sq_cnt, st);
+      launch_exclusive_scan(c->d_sq_cnt, c->d_sq_prefix, nchunk, c->d_sq_scan, c->d_total, st);
+      void **arr[12];
+      swarm_arrays(c->s, arr);
+      for (auto pa : arr) {
+        launch_squeeze_move(*pa, c->d_tmp, c->n, c->d_sq_mask, c->d_sq_prefix, st);
+        void *old = *pa;
+        *pa = (void *)c->d_tmp;
+        c->d_tmp = (double *)old;
+      }
+      c->launches += 4 + 12;
+      c->n = n_alive;
+      JB_CUDA(c, cudaGetLastError());
+      return JB_OK;
+    }
+    cudaGetLastError();  // out of memory for the scratch: squeeze in place instead
+    dfree(c->d_tmp);
+    c->d_tmp = nullptr;
+    c->squeeze_mode = 0;
+  }
   const long long need = std::min(holes, n_alive);
   if (need > c->holes_cap) {
     dfree(c->d_holes);
@@ -939,10 +1016,9 @@ static jb_status sort_by_cell(jb_ctx *c) {
   }
   if (c->n <= 1) return JB_OK;
   if (c->n > 0xffffffffLL) return fail(c, JB_ERR_CAPACITY, "sort supports < 2^32 photons per rank");
-  if (!c->d_tmp) {  // sort scratch is only allocated when sorting is used
-    JB_CUDA(c, dalloc(&c->d_tmp, c->capacity));
-    JB_CUDA(c, dalloc(&c->d_perm, c->capacity));
-  }
+  // scratch is only allocated when it is used (d_tmp also serves the order-preserving squeeze)
+  if (!c->d_tmp) JB_CUDA(c, dalloc(&c->d_tmp, c->capacity));
+  if (!c->d_perm) JB_CUDA(c, dalloc(&c->d_perm, c->capacity));
   StepParams P = make_params(c);
   cudaStream_t st = c->stream;
   JB_CUDA(c, cudaMemsetAsync(c->d_cnt, 0, sizeof(int) * (size_t)c->ncells_local, st));
@@ -1293,11 +1369,13 @@ static jb_status transport_iterations_p2p(jb_ctx *c, double t_start, double dt, 
         launch_transport(P, 0, c->capacity, t_start, dt, c->stream);
       }
       cudaEventRecord(c->it_ev[2 * k + 1], c->stream);
+      tl_mark(c, JB_TL_TRANSPORT);
       P.range = nullptr;
       launch_p2p_push(P, c->d_p2p_state, c->d_peers, c->n_ranks, c->p2p_inbox_cap, c->stream);
       launch_p2p_wait_unpack(P, c->d_p2p_state, c->d_mail, c->d_p2p_inbox[0], c->d_p2p_inbox[1], c->n_ranks,
                              c->p2p_inbox_cap, t_start + dt, ddmc, c->stream);
       c->launches += 6 + (ddmc ? 1 : 0);
+      tl_mark(c, JB_TL_EXCHANGE);
     }
     JB_CUDA(c, cudaMemcpyAsync(c->h_p2p_state, c->d_p2p_state, sizeof(P2PState), cudaMemcpyDeviceToHost, c->stream));
     JB_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -1325,6 +1403,8 @@ jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats
     return fail(c, JB_ERR_COMM, "multi-rank step needs jb_comm_init (or drive the tasks and jb_exchange_* from the host)");
   NvtxRange timestep_range("Jaybenne::Timestep");
   cudaEventRecord(c->ev[0], c->stream);
+  c->tl_n = 0;
+  tl_mark(c, JB_TL_BEGIN);
   jb_status s = JB_OK;
   // a fixed-size pool that also has to take arrivals from other ranks starts the cycle dense (the
   // exchange cannot squeeze the pool between transport iterations)
@@ -1336,8 +1416,10 @@ jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats
   if (s != JB_OK) return s;
   s = jb_update_derived_transport_fields(c, dt);
   if (s != JB_OK) return s;
+  tl_mark(c, JB_TL_FIELDS);
   s = jb_source_photons(c, JB_SOURCE_EMISSION, t_start, dt);
   if (s != JB_OK) return s;
+  tl_mark(c, JB_TL_SOURCE);
   bool done = false;
   long long first = 0;
   float ms_tr = 0.f;
@@ -1360,6 +1442,7 @@ jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats
     s = transport_range(c, first, c->n - first, t_start, dt);
     if (s != JB_OK) return s;
     cudaEventRecord(c->ev[3], c->stream);
+    tl_mark(c, JB_TL_TRANSPORT);
     if (c->n_ranks == 1) {
       s = sync_stats(c);
       if (s != JB_OK) return s;
@@ -1374,6 +1457,7 @@ jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats
     c->exchange_mode = 1;
     s = exchange_nccl(c, t_start + dt, &total_sent);
     if (s != JB_OK) return s;
+    tl_mark(c, JB_TL_EXCHANGE);
     {
       float ms = 0.f;
       cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]);
@@ -1391,10 +1475,13 @@ jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats
   s = check_device_errors(c);
   if (s != JB_OK) return s;
   if (!done) return fail(c, JB_ERR_ITERATIONS, "max_transport_iterations exhausted");
+  tl_mark(c, JB_TL_STATS);
   s = compact(c, (long long)c->h_stats->n_dead);
   if (s != JB_OK) return s;
+  tl_mark(c, JB_TL_SQUEEZE);
   s = jb_evaluate_radiation_energy(c);
   if (s != JB_OK) return s;
+  tl_mark(c, JB_TL_TALLY);
   s = jb_update_fluid(c);
   if (s != JB_OK) return s;
   if (c->cfg.sort_interval > 0 && (++c->cycles_since_sort) >= c->cfg.sort_interval) {
@@ -1403,7 +1490,9 @@ jb_status jb_radiation_step(jb_ctx *c, double t_start, double dt, jb_cycle_stats
     if (s != JB_OK) return s;
   }
   cudaEventRecord(c->ev[1], c->stream);
+  tl_mark(c, JB_TL_END);
   JB_CUDA(c, cudaStreamSynchronize(c->stream));
+  tl_finish(c);
   float ms_total = 0.f;
   cudaEventElapsedTime(&ms_total, c->ev[0], c->ev[1]);
   c->stats.ms_transport = ms_tr;
@@ -1472,6 +1561,17 @@ jb_status jb_get_particles(jb_ctx *c, const jb_particles *d, int64_t capacity, i
 }
 
 int32_t jb_exchange_mode(const jb_ctx *c) { return c ? c->exchange_mode : 0; }
+
+jb_status jb_step_timeline(const jb_ctx *c, int32_t *labels, float *ms, int32_t cap, int32_t *n) {
+  if (!c || !n || cap < 0 || (cap > 0 && (!labels || !ms))) return JB_ERR_INVALID;
+  const int m = c->tl_done < cap ? c->tl_done : cap;
+  for (int q = 0; q < m; ++q) {
+    labels[q] = c->tl_label[q];
+    ms[q] = c->tl_ms[q];
+  }
+  *n = c->tl_done;
+  return JB_OK;
+}
 
 jb_status jb_set_sort_interval(jb_ctx *c, int32_t every_n_cycles) {
   if (!c || every_n_cycles < 0) return JB_ERR_INVALID;

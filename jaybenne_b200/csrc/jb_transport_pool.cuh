@@ -24,6 +24,17 @@
 // Only the block hand-over and the domain boundary conditions (1.5 % of the segments) stay inside the
 // segment phase. Registers hold a photon only for the duration of a phase, so the 148 B of spills of
 // v9 are gone with the per-lane state.
+//
+// v12 — the pool stays ORDERED. A warp owns the 1024-slot chunks it claims, so it writes its census photons
+// back to the FRONT of their chunk, in the order they finish (the k-th photon to retire goes to chunk + k,
+// which the warp's read cursor has already passed), and marks every slot it loads as a hole. After the
+// kernel each chunk holds its survivors packed at the front and holes behind them: nothing ever moves to
+// another chunk, so the (meshblock, cell) order the sourcing kernel laid down only blurs by the few cells a
+// photon travels per cycle, and the per-cell records of a warp's window stay L2-resident cycle after cycle
+// (the tail-into-holes squeeze scattered the last blocks' photons over the whole pool:
+// profiles/r02_v10_bench_cells256.json, continuing run 34 -> 54 ps per segment over 8 cycles against
+// 34 -> 37 ps with a full sort every cycle). Weight and energy now travel through the pool with the photon
+// (their old slot may already hold another photon when they are needed).
 #ifndef JAYBENNE_B200_JB_TRANSPORT_POOL_CUH_
 #define JAYBENNE_B200_JB_TRANSPORT_POOL_CUH_
 
@@ -36,12 +47,13 @@ enum { PS_FREE = 0, PS_READY = 1, PS_PEND = 2, PS_CENSUS = 3, PS_ABS = 4, PS_NON
 template <int S, int NQ>
 struct __align__(16) WarpPool {
   double x[S], y[S], z[S], t[S], vx[S], vy[S], vz[S];
-  double q[NQ][S];   // per-photon factors of the absorption closure (h nu, B_nu prefactor, nu)
+  double w[S];       // weight (energy the photon carries)
+  double q[NQ][S];   // q[0] = photon frequency (swarm field `energy`), q[1] = B_nu prefactor 2 h nu^3 / c^2
   uint2 ida[S];      // (birth index, birth gid)
   uint2 idb[S];      // (source call, draws consumed)
   uint2 carry[S];    // words 2, 3 of Philox block n >> 1 while n is odd (Rng2)
   int2 blk[S];       // (local block, gid)
-  unsigned idx[S];   // swarm slot, relative to `first`
+  unsigned idx[S];   // swarm slot the photon was loaded from, relative to `first` (tells its chunk)
   int cell[S];       // ip | jp << 10 | kp << 20 (interior indices)
   unsigned char st[64];
   unsigned char list[64];
@@ -66,7 +78,7 @@ template <int NDIM, int MINB, bool VALIDATE, int ABS, int S>
 __global__ void __launch_bounds__(POOL_TPB, MINB)
     k_transport_pool(StepParams P, long long first, long long n, double t_start, double dt, int refill_min,
                      int ready_low, int l2_prefetch) {
-  constexpr int NQ = ABS == ABS_GENERIC ? 3 : (ABS == ABS_GRAY_KIRCHHOFF ? 2 : 1);
+  constexpr int NQ = ABS == ABS_GRAY_DIRECT ? 1 : 2;
   static_assert(S > 32 && S <= 64, "two slots per lane");
   __shared__ WarpPool<S, NQ> pools[POOL_WARPS];
   __shared__ unsigned sh_cnt[4];  // crossings, removed in the segment phase (escaped / sent / lost)
@@ -92,8 +104,11 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
   if (threadIdx.x < 4) sh_cnt[threadIdx.x] = 0u;
   __syncthreads();
 
-  // the warp's chunk of swarm slots (warp-uniform)
-  unsigned cur = 0, end = 0;
+  // the warp's chunks of swarm slots (warp-uniform): the one being read, and the one before it, whose last
+  // photons may still be in flight. Slot offsets are relative to `first`.
+  unsigned cur = 0, end = 0;    // read cursor and end of the current chunk
+  unsigned c_base = 0, wr = 0;  // current chunk: first slot and write cursor (wr <= cur: only slots already read)
+  unsigned p_wr = 0;            // write cursor of the previous chunk (all of its slots have been read)
   bool exhausted = false;
   bool flip = false;
   unsigned c_seg = 0, c_scat = 0, c_abs = 0, bad = 0;
@@ -109,7 +124,16 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
     const unsigned w1 = __ballot_sync(FULL, s1 == PS_CENSUS || s1 == PS_ABS);
     const int n_ready = __popc(r0) + __popc(r1), n_pend = __popc(q0) + __popc(q1);
     const int n_ret = __popc(w0) + __popc(w1), n_nonlive = n_ret + __popc(f0) + __popc(f1);
-    const bool input_left = cur < end || !exhausted;
+    // two write cursors are kept, so the next chunk is claimed only once the chunk BEFORE the current one has
+    // no photon left in the pool (a chunk is >= 16 refills long: by then they have all retired, except in
+    // media where single histories run to hundreds of segments)
+    bool can_claim = !exhausted;
+    if (cur >= end && can_claim) {
+      const bool old0 = s0 != PS_FREE && W.idx[lane] < c_base;
+      const bool old1 = s1 != PS_FREE && s1 != PS_NONE && W.idx[lane + 32u] < c_base;
+      can_claim = !__any_sync(FULL, old0 || old1);
+    }
+    const bool input_left = cur < end || can_claim;
     const bool idle = n_ready + n_pend == 0;
 
     // =====================================================================================
@@ -118,28 +142,33 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
     if ((n_nonlive >= refill_min || idle) && (input_left || n_ret > 0)) {
       int cnt;
       const int s = pool_pick(W.list, input_left ? (w0 | f0) : w0, input_left ? (w1 | f1) : w1, false, lane, lt, cnt);
-      if (s >= 0) {
-        const int old = W.st[s];
-        if (old == PS_CENSUS) {
-          // the photon reached t_end: back to the swarm arrays (what the reference's loop leaves in place)
-          const long long idx = first + (long long)W.idx[s];
+      {
+        const int old = s >= 0 ? (int)W.st[s] : PS_FREE;
+        // the photon reached t_end (the reference's loop leaves it in place): back to the swarm arrays, packed
+        // at the front of the chunk it came from — position = the chunk's write cursor + rank among the lanes
+        const bool cen = old == PS_CENSUS;
+        const bool in_cur = cen && W.idx[s] >= c_base;
+        const unsigned m_cur = __ballot_sync(FULL, in_cur), m_prev = __ballot_sync(FULL, cen && !in_cur);
+        if (cen) {
+          const long long idx = first + (long long)(in_cur ? wr + __popc(m_cur & lt) : p_wr + __popc(m_prev & lt));
           const int cl = W.cell[s];
-          const uint2 ib = W.idb[s];
           P.s.x[idx] = W.x[s]; P.s.y[idx] = W.y[s]; P.s.z[idx] = W.z[s]; P.s.t[idx] = W.t[s];
           P.s.vx[idx] = W.vx[s]; P.s.vy[idx] = W.vy[s]; P.s.vz[idx] = W.vz[s];
+          P.s.w[idx] = W.w[s]; P.s.e[idx] = W.q[0][s];
           P.s.loc[idx] = make_int2(W.blk[s].x, (((cl >> 20) & 1023) * nx2 + ((cl >> 10) & 1023)) * nx1 + (cl & 1023));
-          P.s.idb[idx] = ib;
+          P.s.ida[idx] = W.ida[s];
+          P.s.idb[idx] = W.idb[s];
         } else if (old == PS_ABS) {
-          // absorbed (transport.cpp:157-163): deposit, mark the particle for removal
-          const long long idx = first + (long long)W.idx[s];
+          // absorbed (transport.cpp:157-163): deposit; the particle's slot became a hole when it was loaded
           const int cl = W.cell[s];
-          const double ww = P.s.w[idx];
+          const double ww = W.w[s];
           atomicAdd(&P.f.edelta[(long long)W.blk[s].x * m.ncell +
                                 ((long long)((cl >> 20) & 1023) * nx2 + ((cl >> 10) & 1023)) * nx1 + (cl & 1023)], ww);
-          P.s.loc[idx].x = -1;
           e_abs += ww;
           c_abs++;
         }
+        wr += (unsigned)__popc(m_cur);
+        p_wr += (unsigned)__popc(m_prev);
       }
       // the next photons of the warp's chunk
       bool in_chunk = false;
@@ -152,7 +181,9 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
           if ((long long)c0 >= n) {
             exhausted = true;
           } else {
+            p_wr = wr;  // the chunk just read becomes the previous one
             cur = (unsigned)c0;
+            c_base = wr = cur;
             end = (long long)c0 + IMC_CHUNK > n ? (unsigned)n : cur + IMC_CHUNK;
           }
         }
@@ -181,20 +212,19 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
         const double t0 = ld_once(&P.s.t[my]);
         const double l_x = ld_once(&P.s.x[my]), l_y = ld_once(&P.s.y[my]), l_z = ld_once(&P.s.z[my]);
         const double l_vx = ld_once(&P.s.vx[my]), l_vy = ld_once(&P.s.vy[my]), l_vz = ld_once(&P.s.vz[my]);
-        const double l_e = ABS == ABS_GRAY_DIRECT ? 0.0 : ld_once(&P.s.e[my]);
+        const double l_e = ld_once(&P.s.e[my]), l_w = ld_once(&P.s.w[my]);
         const uint2 ia = ld_once(&P.s.ida[my]), ib = ld_once(&P.s.idb[my]);
-        // census photons of an earlier iteration are skipped (transport.cpp:98)
-        if (lc.x >= 0 && t0 < t_end) {
+        if (lc.x >= 0) {
+          // the photon lives in the pool from here on and its slot is a hole; one that is already at census
+          // (transport.cpp:98 skips it) only passes through to be packed with the others
+          P.s.loc[my] = make_int2(-1, 0);
           W.idx[s] = my32;
           W.t[s] = t0;
           W.x[s] = l_x; W.y[s] = l_y; W.z[s] = l_z;
           W.vx[s] = l_vx; W.vy[s] = l_vy; W.vz[s] = l_vz;
-          if (ABS != ABS_GRAY_DIRECT) {
-            const PhotonFreq q = photon_freq(P.cl, l_e);
-            W.q[0][s] = q.hnu;
-            W.q[NQ > 1 ? 1 : 0][s] = q.bpref;
-            if (NQ > 2) W.q[NQ - 1][s] = q.f;
-          }
+          W.w[s] = l_w;
+          W.q[0][s] = l_e;
+          if (NQ > 1) W.q[NQ - 1][s] = photon_freq(P.cl, l_e).bpref;
           W.ida[s] = ia;
           W.idb[s] = ib;
           // an odd draw counter carries the second half of block n >> 1 (Rng2)
@@ -230,7 +260,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
             xtoijk<NDIM>(B, pv, ti, tj, tk);
             if (ti != ip || tj != jp || tk != kp) atomicAdd(&P.stats->n_validate, 1ull);
           }
-          newst = PS_READY;
+          newst = t0 < t_end ? PS_READY : PS_CENSUS;
         }
       }
       if (s >= 0) W.st[s] = (unsigned char)newst;
@@ -304,7 +334,8 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
         c.aa = ((P.cl.rho_unit * cp.rho) * P.cl.kappa) * P.cl.length_unit;
       } else if (ABS == ABS_GRAY_KIRCHHOFF) {
         // absorption_coeff_hoisted() with the gray branch fixed
-        const double hnu = W.q[0][s], bpref = W.q[NQ > 1 ? 1 : 0][s];
+        // h nu as photon_freq() forms it (nu * freq_unit, then * h): two multiplies instead of 8 bytes per slot
+        const double hnu = P.cl.h * (W.q[0][s] * P.cl.freq_unit), bpref = W.q[NQ - 1][s];
         const double r = P.cl.rho_unit * cp.rho, T = P.cl.temp_unit * cp.temp;
         const double x = hnu / (P.cl.kb * T);
         const double Bnu = bpref / jbm::expm1(x);
@@ -312,7 +343,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
         c.aa = robust_ratio_pos(jnu, Bnu) * P.cl.length_unit;
       } else {
         PhotonFreq q;
-        q.hnu = W.q[0][s]; q.bpref = W.q[NQ > 1 ? 1 : 0][s]; q.f = W.q[NQ - 1][s];
+        q.f = W.q[0][s] * P.cl.freq_unit; q.hnu = P.cl.h * q.f; q.bpref = W.q[NQ - 1][s];
         c.aa = absorption_coeff_hoisted(P.cl, cp.rho, cp.temp, q);
       }
       bool is_absorbed = false, is_scattered = false;
@@ -329,14 +360,13 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
       int newst = PS_READY;
       if (!on_block(m, p.ip, p.jp, p.kp)) {
         // ---- left the meshblock: swarm BCs + hand-over (MeshSend / MeshReceive on device) ----
-        const long long idx = first + (long long)W.idx[s];
         const int bx = p.ip < 0 ? -1 : (p.ip >= nx1 ? 1 : 0);
         const int by = p.jp < 0 ? -1 : (p.jp >= nx2 ? 1 : 0);
         const int bz = p.kp < 0 ? -1 : (p.kp >= nx3 ? 1 : 0);
         bool gone = false;
         if (!apply_swarm_bc<NDIM>(m, p)) {
           atomicAdd(&P.stats->n_escaped, 1ull);
-          atomicAdd(&P.ebins[EB_ESCAPED * EBINS + (unsigned)(gw & (EBINS - 1))], P.s.w[idx]);
+          atomicAdd(&P.ebins[EB_ESCAPED * EBINS + (unsigned)(gw & (EBINS - 1))], W.w[s]);
           gone = true;
         } else {
           int ngid = __ldg(&m.nbr[lb * 27 + (bz + 1) * 9 + (by + 1) * 3 + (bx + 1)]);
@@ -371,7 +401,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
               const unsigned long long slot = atomicAdd(&P.out.count[nb.rank], 1ull);
               if ((long long)slot < P.out.cap) {
                 ExRecord r;
-                r.x = p.x; r.y = p.y; r.z = p.z; r.t = p.t; r.w = P.s.w[idx]; r.e = P.s.e[idx];
+                r.x = p.x; r.y = p.y; r.z = p.z; r.t = p.t; r.w = W.w[s]; r.e = W.q[0][s];
                 r.vx = p.vx; r.vy = p.vy; r.vz = p.vz;
                 r.rng[0] = rng.id0; r.rng[1] = rng.id1; r.rng[2] = rng.id2; r.rng[3] = rng.n;
                 r.dest_gid = ngid;
@@ -394,8 +424,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
             }
           }
         }
-        if (gone) {
-          P.s.loc[idx].x = -1;
+        if (gone) {  // (its slot became a hole when it was loaded)
           atomicAdd(&sh_cnt[1], 1u);
           newst = PS_FREE;
         } else {

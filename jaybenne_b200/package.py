@@ -268,6 +268,15 @@ class Jaybenne:
         """0 none, 1 NCCL send/recv per iteration, 2 direct peer stores over NVLink (jb_exchange_mode)"""
         return int(self.api.exchange_mode(self._ctx))
 
+    TL_NAMES = {1: "fields", 2: "source", 3: "transport", 4: "exchange", 5: "stats", 6: "squeeze", 7: "tally", 8: "end"}
+
+    def step_timeline(self):
+        """[(phase name, ms), ...] of the last RadiationStep in stream order (jb_step_timeline)."""
+        cap = 96
+        labels, ms, n = (C.c_int32 * cap)(), (C.c_float * cap)(), C.c_int32(0)
+        self._check(self.api.step_timeline(self._ctx, labels, ms, cap, C.byref(n)))
+        return [(self.TL_NAMES.get(labels[q], str(labels[q])), float(ms[q])) for q in range(min(n.value, cap))]
+
     def set_sort_interval(self, every_n_cycles: int):
         self._check(self.api.set_sort_interval(self._ctx, int(every_n_cycles)))
 

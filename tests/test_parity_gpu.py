@@ -338,6 +338,33 @@ def test_cell_sorted_pool_gives_identical_results():
     assert len(key) == sg["n_end"] and np.all(np.diff(key) >= 0), "pool is not sorted by (block, cell)"
 
 
+def test_pool_stays_ordered_through_transport_and_squeeze():
+    """k_transport_pool packs a chunk's survivors at the front of that chunk and the squeeze (k_squeeze_*) keeps the
+    relative order of the live photons: a photon never overtakes one that was sourced >= 2 chunks (2048 slots)
+    ahead of it, cycle after cycle — the (meshblock, cell) order of the sourcing pass only blurs locally. With
+    do_emission off nothing is appended, so the thermal photons' birth slot is their rank in (block, birth index)."""
+    text = pu.synthetic_text(n=16, nb=8, num_particles=60000, do_emission=False)
+    gpu, ora = pu.make_pair(text=text)
+    gpu.ProblemGenerator(pu.synthetic_density); ora.ProblemGenerator(pu.synthetic_density)
+    p0 = gpu.jb.particles()
+    rid0 = p0["rng"].astype(np.int64)
+    # birth slot of (birth index, birth gid): the position straight after sourcing
+    birth = {(int(a), int(b)): q for q, (a, b) in enumerate(zip(rid0[:, 0], rid0[:, 1]))}
+    n0 = len(rid0)
+    for cyc in range(3):
+        sg, so = gpu.Step(), ora.Step()
+        for k in pu.COUNT_KEYS:   # (energy sums of 60000 equal weights: the oracle's serial sum is the noisier one)
+            assert sg[k] == so[k], (k, sg[k], so[k])
+        p = gpu.jb.particles()   # squeezes (order-preserving) and reads the pool in slot order
+        rid = p["rng"].astype(np.int64)
+        assert len(rid) == sg["n_end"] and sg["n_end"] < n0
+        slot = np.array([birth[(int(a), int(b))] for a, b in zip(rid[:, 0], rid[:, 1])])
+        chunk = slot // 1024
+        # non-decreasing birth chunk along the pool: a chunk's photons stay together and chunks stay in order
+        assert np.all(np.diff(chunk) >= 0), f"cycle {cyc}: the pool lost its order"
+    pu.assert_swarm_equal(gpu.jb, ora.jb)
+
+
 def test_range_test_free_division_is_the_ieee_quotient():
     """jbm::div_normal (nvcc's fast-path sequence without the operand test and slow-path call) must return the
     correctly rounded quotient, i.e. the bits of `/`, over the operand ranges the kernels use it on."""
