@@ -378,10 +378,107 @@ void launch_exclusive_scan(const int *cnt, long long *prefix, long long n, long 
 // cell's new photons so the SoA stores coalesce. Photon `np` (its index in the block's
 // prefix order) keys its random stream, so the result does not depend on the schedule.
 // ---------------------------------------------------------------------------------------
+// one new photon: the stream's draws #0..#10 in the reference's order (sourcing.cpp:175-198): x y | z mu |
+// phi xi0 | xi1 xi2 | xi3 xi4 | t — one Philox block per pair, straight-line (same values as Rng::drand)
+__device__ __forceinline__ void source_one(const StepParams &P, const DBlock &b, const int lb, const int ci,
+                                           const double xi, const double yi, const double zi, const double temp,
+                                           const double ew, const int np, const long long slot, const int source_type,
+                                           const double t_start, const double dt, const uint32_t call) {
+  const double vv = P.cl.c_code, sb = P.cl.sb_code;
+  const uint32_t id0 = (uint32_t)np, id1 = (uint32_t)b.gid;
+  double d0, d1, d2, d3, d4, d5, d6, d7, d8, d9;
+  philox_pair(0u, id0, id1, call, P.rk, d0, d1);
+  philox_pair(1u, id0, id1, call, P.rk, d2, d3);
+  philox_pair(2u, id0, id1, call, P.rk, d4, d5);
+  philox_pair(3u, id0, id1, call, P.rk, d6, d7);
+  philox_pair(4u, id0, id1, call, P.rk, d8, d9);
+  const double x = xi + b.dx[0] * (d0 - 0.5);
+  const double y = yi + b.dx[1] * (d1 - 0.5);
+  const double z = zi + b.dx[2] * (d2 - 0.5);
+  const double theta = jbm::acos(2.0 * d3 - 1.0);
+  const double phi = 2.0 * JB_PI * d4;
+  double st, ct, sp, cp;
+  jbm::sincos(theta, &st, &ct);
+  jbm::sincos(phi, &sp, &cp);
+  const double energy = planck_energy_draws(P.cl, d5, d6, d7, d8, d9, sb, temp);
+  double tp = 0.;
+  uint32_t ndraws = 10u;
+  if (source_type == JB_SOURCE_EMISSION) {
+    double d10, d11;
+    philox_pair(5u, id0, id1, call, P.rk, d10, d11);
+    tp = t_start + d10 * dt;
+    ndraws = 11u;
+  }
+  P.s.x[slot] = x;
+  P.s.y[slot] = y;
+  P.s.z[slot] = z;
+  P.s.vx[slot] = vv * st * cp;
+  P.s.vy[slot] = vv * st * sp;
+  P.s.vz[slot] = vv * ct;
+  P.s.e[slot] = energy;
+  P.s.w[slot] = ew;
+  P.s.t[slot] = tp;
+  P.s.loc[slot] = make_int2(lb, ci);
+  P.s.ida[slot] = make_uint2((uint32_t)np, (uint32_t)b.gid);
+  P.s.idb[slot] = make_uint2(call, ndraws);
+}
+
+// Sparse launches (an emission pass that gives most cells no photon or one): one THREAD per new photon, which
+// finds its cell in the prefix array by bisection; the per-cell energy_delta reset / debit (sourcing.cpp:165-166)
+// is a thread-per-cell pass of its own. The warp-per-cell kernel below spent a warp's trip on every cell — 16.7 M
+// trips for 2 M photons in the 256^3 benchmark's emission pass (profiles/r02_ncu_source_emit_emission_cells128.md).
+__global__ void __launch_bounds__(256) k_source_debit(StepParams P, int first_local, long long ncells, int source_type) {
+  const long long base = (long long)first_local * P.mesh.ncell;
+  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < ncells; q += (long long)gridDim.x * blockDim.x) {
+    const long long c = base + q;
+    double dejbn = 0.0;
+    if (source_type == JB_SOURCE_EMISSION) {
+      // debited serially so the sum rounds exactly as the reference's per-cell loop does
+      const int npart = (int)round(P.f.src_num[c]);
+      const double ew = P.f.src_ew[c];
+      for (int np = 0; np < npart; ++np) dejbn -= ew;
+    }
+    P.f.edelta[c] = dejbn;
+  }
+}
+__global__ void __launch_bounds__(256, 4) k_source_emit_sparse(StepParams P, int first_local, long long ncells, int source_type,
+                                                               double t_start, double dt, uint32_t call,
+                                                               const long long *__restrict__ prefix, long long slot0,
+                                                               long long total) {
+  const DMesh &m = P.mesh;
+  unsigned long long my_n = 0;
+  double my_e = 0.0;
+  for (long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x; p < total; p += (long long)gridDim.x * blockDim.x) {
+    // the last cell q with prefix[q] <= p (empty cells share their successor's offset, so this is p's cell)
+    long long lo = 0, hi = ncells - 1;
+    while (lo < hi) {
+      const long long mid = (lo + hi + 1) >> 1;
+      if (__ldg(&prefix[mid]) <= p) lo = mid; else hi = mid - 1;
+    }
+    const long long q = lo;
+    const int lbq = (int)(q / m.ncell);
+    const int lb = first_local + lbq;
+    const int ci = (int)(q - (long long)lbq * m.ncell);
+    const long long c = (long long)lb * m.ncell + ci;
+    const long long pglobal = __ldg(&prefix[q]);
+    const int np = (int)(p - __ldg(&prefix[(long long)lbq * m.ncell]));  // index in the block's prefix order
+    const DBlock &b = m.blocks[m.local_gid[lb]];
+    const int i = ci % m.nxb[0], j = (ci / m.nxb[0]) % m.nxb[1], k = ci / (m.nxb[0] * m.nxb[1]);
+    const double xi = cell_center(b, m.ng[0], 0, i), yi = cell_center(b, m.ng[1], 1, j), zi = cell_center(b, m.ng[2], 2, k);
+    const double temp = eos_temperature(P.cl, P.f.sie[c]);
+    const double ew = P.f.src_ew[c];
+    (void)pglobal;
+    source_one(P, b, lb, ci, xi, yi, zi, temp, ew, np, slot0 + p, source_type, t_start, dt, call);
+    my_n += 1;
+    my_e += ew;
+  }
+  warp_add_u64(&P.stats->n_sourced, my_n);
+  warp_add_energy(P, EB_SOURCED, my_e);
+}
+
 __global__ void __launch_bounds__(256, 4) k_source_emit(StepParams P, int first_local, long long ncells, int source_type, double t_start,
                               double dt, uint32_t call, const long long *prefix, long long slot0) {
   const DMesh &m = P.mesh;
-  const double vv = P.cl.c_code, sb = P.cl.sb_code;
   const int lane = threadIdx.x & 31;
   // 32-bit cell arithmetic: a rank holds < 2^31 cells (checked by the launcher), and the 64-bit divide /
   // modulo this loop used to do per cell were ~1/3 of the kernel's instructions (profiles/r02_ncu_source_emit*.md)
@@ -417,44 +514,7 @@ __global__ void __launch_bounds__(256, 4) k_source_emit(StepParams P, int first_
     for (int o = lane; o < npart; o += 32) {
       const int np = pstart + o;
       const long long slot = slot0 + pglobal + o;
-      // the photon's stream, draws #0..#10 in the reference's order (sourcing.cpp:175-198): x y | z mu |
-      // phi xi0 | xi1 xi2 | xi3 xi4 | t — one Philox block per pair, straight-line (same values as Rng::drand)
-      const uint32_t id0 = (uint32_t)np, id1 = (uint32_t)b.gid;
-      double d0, d1, d2, d3, d4, d5, d6, d7, d8, d9;
-      philox_pair(0u, id0, id1, call, P.rk, d0, d1);
-      philox_pair(1u, id0, id1, call, P.rk, d2, d3);
-      philox_pair(2u, id0, id1, call, P.rk, d4, d5);
-      philox_pair(3u, id0, id1, call, P.rk, d6, d7);
-      philox_pair(4u, id0, id1, call, P.rk, d8, d9);
-      const double x = xi + b.dx[0] * (d0 - 0.5);
-      const double y = yi + b.dx[1] * (d1 - 0.5);
-      const double z = zi + b.dx[2] * (d2 - 0.5);
-      const double theta = jbm::acos(2.0 * d3 - 1.0);
-      const double phi = 2.0 * JB_PI * d4;
-      double st, ct, sp, cp;
-      jbm::sincos(theta, &st, &ct);
-      jbm::sincos(phi, &sp, &cp);
-      const double energy = planck_energy_draws(P.cl, d5, d6, d7, d8, d9, sb, temp);
-      double tp = 0.;
-      uint32_t ndraws = 10u;
-      if (source_type == JB_SOURCE_EMISSION) {
-        double d10, d11;
-        philox_pair(5u, id0, id1, call, P.rk, d10, d11);
-        tp = t_start + d10 * dt;
-        ndraws = 11u;
-      }
-      P.s.x[slot] = x;
-      P.s.y[slot] = y;
-      P.s.z[slot] = z;
-      P.s.vx[slot] = vv * st * cp;
-      P.s.vy[slot] = vv * st * sp;
-      P.s.vz[slot] = vv * ct;
-      P.s.e[slot] = energy;
-      P.s.w[slot] = ew;
-      P.s.t[slot] = tp;
-      P.s.loc[slot] = make_int2(lb, ci);
-      P.s.ida[slot] = make_uint2((uint32_t)np, (uint32_t)b.gid);
-      P.s.idb[slot] = make_uint2(call, ndraws);
+      source_one(P, b, lb, ci, xi, yi, zi, temp, ew, np, slot, source_type, t_start, dt, call);
       my_n += 1;
       my_e += ew;
     }
@@ -954,7 +1014,8 @@ void launch_source_count(const StepParams &P, int first_local, int nlocal_call, 
   k_source_count<<<grid_for(ncells, 256), 256, 0, st>>>(P, first_local, ncells, source_type, dt, npc, call, cnt);
 }
 void launch_source_emit(const StepParams &P, int first_local, int nlocal_call, int source_type, double t_start,
-                        double dt, uint32_t call, const long long *prefix, long long slot0, cudaStream_t st) {
+                        double dt, uint32_t call, const long long *prefix, long long slot0, long long total,
+                        cudaStream_t st) {
   const long long ncells = (long long)nlocal_call * P.mesh.ncell;
   if (ncells <= 0) return;
   // cumulative j^-4 table of the Planck sampler: once per device, the reference's running sum
@@ -973,6 +1034,14 @@ void launch_source_emit(const StepParams &P, int first_local, int nlocal_call, i
     cudaMemcpyToSymbolAsync(d_planck_cum, cum, sizeof(cum), 0, cudaMemcpyHostToDevice, st);
     cudaStreamSynchronize(st);
     table_ready[dev] = true;
+  }
+  if (total < 4 * ncells) {
+    // fewer than 4 photons per cell on average: thread per photon + thread per cell (k_source_emit_sparse)
+    k_source_debit<<<grid_for(ncells, 256), 256, 0, st>>>(P, first_local, ncells, source_type);
+    if (total > 0)
+      k_source_emit_sparse<<<grid_for(total, 256), 256, 0, st>>>(P, first_local, ncells, source_type, t_start, dt, call,
+                                                                  prefix, slot0, total);
+    return;
   }
   // one warp per cell, 8 warps per CTA
   k_source_emit<<<grid_for(ncells * 32, 256), 256, 0, st>>>(P, first_local, ncells, source_type, t_start, dt, call,
@@ -1509,13 +1578,13 @@ __global__ void k_p2p_unpack(StepParams P, const P2PState *st, const ExRecord *i
 void launch_p2p_push(const StepParams &P, P2PState *state, const P2PPeers *peers, int n_ranks, long long inbox_cap,
                      cudaStream_t st) {
   k_p2p_reserve<<<1, P2P_MAX_RANKS, 0, st>>>(P, state, peers, n_ranks, inbox_cap);
-  k_p2p_copy<<<dim3(32, (unsigned)n_ranks), 256, 0, st>>>(P, state, peers);
+  k_p2p_copy<<<dim3(148, (unsigned)n_ranks), 256, 0, st>>>(P, state, peers);  // CTAs of a peer with nothing to send exit at once
   k_p2p_signal<<<1, P2P_MAX_RANKS, 0, st>>>(P, state, peers, n_ranks);
 }
 void launch_p2p_wait_unpack(const StepParams &P, P2PState *state, P2PMail *my_mail, ExRecord *inbox0, ExRecord *inbox1,
                             int n_ranks, long long inbox_cap, double t_end, bool ddmc, cudaStream_t st) {
   k_p2p_wait<<<1, P2P_MAX_RANKS, 0, st>>>(P, state, my_mail, n_ranks, inbox_cap);
-  k_p2p_unpack<<<148, 128, 0, st>>>(P, state, inbox0, inbox1, t_end);
+  k_p2p_unpack<<<148 * 8, 256, 0, st>>>(P, state, inbox0, inbox1, t_end);
   if (ddmc && P.mesh.ndim >= 2) {
     StepParams Q = P;
     Q.range = state->range;  // address of the device-side (first, n)

@@ -165,7 +165,8 @@ void launch_exclusive_scan(const int *cnt, long long *prefix, long long n, long 
                            long long *total, cudaStream_t st);
 long long scan_scratch_elems(long long n);
 void launch_source_emit(const StepParams &P, int first_local, int nlocal_call, int source_type, double t_start,
-                        double dt, uint32_t call, const long long *prefix, long long slot0, cudaStream_t st);
+                        double dt, uint32_t call, const long long *prefix, long long slot0, long long total,
+                        cudaStream_t st);
 void launch_transport(const StepParams &P, long long first, long long n, double t_start, double dt,
                       cudaStream_t st);
 // knobs of the persistent IMC kernel (jb_lib.cu reads them from the environment once)

@@ -867,8 +867,8 @@ static jb_status source_photons(jb_ctx *c, int first, int nb, int source_type, d
     P = make_params(c);
   }
   c->census_valid = false;
-  launch_source_emit(P, first, nb, source_type, t_start, dt, call, c->d_prefix, c->n, c->stream);
-  c->launches += 1;
+  launch_source_emit(P, first, nb, source_type, t_start, dt, call, c->d_prefix, c->n, total, c->stream);
+  c->launches += total < 4 * ncells ? (total > 0 ? 2 : 1) : 1;
   c->n += total;
   JB_CUDA(c, cudaGetLastError());
   return JB_OK;

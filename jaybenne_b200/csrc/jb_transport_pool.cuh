@@ -175,16 +175,28 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
       unsigned my32 = 0;
       if (input_left) {
         if (cur >= end) {
+          // guided claim: IMC_CHUNK slots while plenty remain, smaller pieces towards the end of the range (a
+          // piece = what is left / twice the warps, at least 64), so that the last warps finish together — a short
+          // range (the arrivals of a later exchange iteration, a rank's 1/8 of the pool) otherwise ran on a few
+          // warps with 1024 photons each (profiles/r02_v12_bench_cells256_gpus8_*.json: iterations 3+ of a cycle).
+          // The look at the counter is only a hint; the atomic add is the claim.
           unsigned long long c0 = 0;
-          if (lane == 0) c0 = atomicAdd(P.work, (unsigned long long)IMC_CHUNK);
+          unsigned piece = IMC_CHUNK;
+          if (lane == 0) {
+            const long long seen = (long long)*(volatile unsigned long long *)P.work;
+            const long long left = n - seen, share = left / (2ll * (long long)gridDim.x * POOL_WARPS);
+            if (share < IMC_CHUNK) piece = share < 64 ? 64u : ((unsigned)share & ~31u);
+            c0 = atomicAdd(P.work, (unsigned long long)piece);
+          }
           c0 = __shfl_sync(FULL, c0, 0);
+          piece = __shfl_sync(FULL, piece, 0);
           if ((long long)c0 >= n) {
             exhausted = true;
           } else {
             p_wr = wr;  // the chunk just read becomes the previous one
             cur = (unsigned)c0;
             c_base = wr = cur;
-            end = (long long)c0 + IMC_CHUNK > n ? (unsigned)n : cur + IMC_CHUNK;
+            end = (long long)c0 + piece > n ? (unsigned)n : cur + piece;
           }
         }
         if (cur < end) {
