@@ -904,6 +904,7 @@ static void launch_transport_nd(const StepParams &P, long long first, long long 
 #include "jb_transport_imc.cuh"
 #include "jb_transport_pool.cuh"
 #include "jb_transport_ddmc.cuh"
+#include "jb_transport_hpool.cuh"
 
 void launch_transport(const StepParams &P, long long first, long long n, double t_start, double dt,
                       cudaStream_t st) {
@@ -926,6 +927,15 @@ void launch_transport(const StepParams &P, long long first, long long n, double 
       default: launch_transport_imc<3>(P, first, n, t_start, dt, st); break;
     }
     return;
+  }
+  if (dd && g_tuning.variant == 2) {  // hybrid IMC / DDMC on warp-private photon pools
+    bool ok;
+    switch (P.mesh.ndim) {
+      case 1: ok = launch_transport_hpool<1>(P, first, n, t_start, dt, st); break;
+      case 2: ok = launch_transport_hpool<2>(P, first, n, t_start, dt, st); break;
+      default: ok = launch_transport_hpool<3>(P, first, n, t_start, dt, st); break;
+    }
+    if (ok) return;
   }
   if (dd && g_tuning.variant >= 1) {  // hybrid IMC / DDMC: persistent warps with lane refill
     switch (P.mesh.ndim) {

@@ -181,6 +181,7 @@ void set_transport_tuning(const TransportTuning &t);
 bool transport_takes_device_range(const StepParams &P);
 void set_pool_tuning(int slots, int refill_min, int ready_low);
 void set_pool_prefetch(int on);
+void set_pool_fixed_chunk(int on);
 void launch_pack_props(const StepParams &P, cudaStream_t st);
 // folds ebins[kind] into *dst (dst = &stats->e_* or the census scratch)
 void launch_fold_bins(const StepParams &P, int kind, double *dst, cudaStream_t st);

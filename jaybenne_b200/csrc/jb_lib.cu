@@ -416,6 +416,7 @@ jb_status jb_create(const jb_config *cfg, jb_ctx **out) {
       if (const char *v = getenv("JB_POOL_READY_LOW")) prl = atoi(v);
       set_pool_tuning(ps, prf, prl);
       if (const char *v = getenv("JB_POOL_PREFETCH")) set_pool_prefetch(atoi(v));
+      if (const char *v = getenv("JB_POOL_FIXED_CHUNK")) set_pool_fixed_chunk(atoi(v));
     }
   }
   *out = c;

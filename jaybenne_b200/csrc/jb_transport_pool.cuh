@@ -185,7 +185,8 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
           if (lane == 0) {
             const long long seen = (long long)*(volatile unsigned long long *)P.work;
             const long long left = n - seen, share = left / (2ll * (long long)gridDim.x * POOL_WARPS);
-            if (share < IMC_CHUNK) piece = share < 64 ? 64u : ((unsigned)share & ~31u);
+            if (share < IMC_CHUNK && !(l2_prefetch & 2))  // (bit 1: fixed pieces, JB_POOL_FIXED_CHUNK, for A/B runs)
+              piece = share < 64 ? 64u : ((unsigned)share & ~31u);
             c0 = atomicAdd(P.work, (unsigned long long)piece);
           }
           c0 = __shfl_sync(FULL, c0, 0);
@@ -203,7 +204,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
           my32 = cur + lane;
           in_chunk = s >= 0 && my32 < end;
           cur = min(end, cur + (unsigned)cnt);
-          if (l2_prefetch && lane < 11u && cur < end) {
+          if ((l2_prefetch & 1) && lane < 11u && cur < end) {
             // the window the NEXT refill will read, pulled into L2 by the bulk-copy (TMA) unit while this
             // one's photons run: one cp.async.bulk.prefetch.L2 per swarm array (16-byte aligned, 256 B)
             const double *arr = lane == 0 ? P.s.x : lane == 1 ? P.s.y : lane == 2 ? P.s.z : lane == 3 ? P.s.t
@@ -484,7 +485,8 @@ struct PoolTuning {
   int l2_prefetch;  // 1: cp.async.bulk.prefetch.L2 of the next refill window (JB_POOL_PREFETCH; measured)
 };
 static PoolTuning g_pool = {64, 24, 32, 0};
-void set_pool_prefetch(int on) { g_pool.l2_prefetch = on ? 1 : 0; }
+void set_pool_prefetch(int on) { g_pool.l2_prefetch = (g_pool.l2_prefetch & ~1) | (on ? 1 : 0); }
+void set_pool_fixed_chunk(int on) { g_pool.l2_prefetch = (g_pool.l2_prefetch & ~2) | (on ? 2 : 0); }
 void set_pool_tuning(int slots, int refill_min, int ready_low) {
   g_pool.slots = slots == 64 ? 64 : 56;
   g_pool.refill_min = max(1, min(refill_min, 32));

@@ -46,7 +46,7 @@ def main():
     top = int(sys.argv[3]) if len(sys.argv) > 3 else 60
     by_samples = len(sys.argv) > 4 and sys.argv[4] == "samples"   # rank the lines by stall samples instead
     lines = sass_lines(pat)
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+    raw = (open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout)
     rows = list(csv.reader(raw.splitlines()))
     hdr = next(r for r in rows if r and r[0] == "Address")
     body = [r for r in rows if len(r) == len(hdr) and r[0].startswith("0x")]

@@ -3,7 +3,7 @@ sys.path.insert(0,'/root/repo/tools')
 import ncu_lines as nl
 rep, pat = sys.argv[1], sys.argv[2]
 lines = nl.sass_lines(pat)
-raw = subprocess.run(["ncu","-i",rep,"--page","source","--csv"],capture_output=True,text=True).stdout
+raw = (open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout)
 rows=list(csv.reader(raw.splitlines()))
 hdr=next(r for r in rows if r and r[0]=="Address")
 body=[r for r in rows if len(r)==len(hdr) and r[0].startswith("0x")]

@@ -29,7 +29,7 @@ KEEP = [
 def main():
     rep = sys.argv[1]
     row = int(sys.argv[2]) if len(sys.argv) > 2 else 0
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    raw = (open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout)
     rows = list(csv.reader(raw.splitlines()))
     hdr, units, vals = rows[0], rows[1], rows[2 + row]
     d = {h: (u, v) for h, u, v in zip(hdr, units, vals)}
