@@ -293,7 +293,7 @@ static __constant__ double d_planck_cum[100];
 __device__ __forceinline__ double planck_energy_draws(const Closure &cl, const double xi0, const double xi1,
                                                       const double xi2, const double xi3, const double xi4,
                                                       const double sb, const double temp) {
-  const double rhs = xi0 * cl.pi4 / 90.0;
+  const double rhs = jbm::div_normal(xi0 * cl.pi4, 90.0);  // (numerator 0 or >= 1e-14: the IEEE quotient)
   int l = 1;
   double ll = 1.0;
   while (l < 100) {
@@ -303,7 +303,7 @@ __device__ __forceinline__ double planck_energy_draws(const Closure &cl, const d
     }
     l++;
   }
-  return -(1.0 / ll) * jbm::log(xi1 * xi2 * xi3 * xi4) * sb * temp;
+  return -jbm::div_normal(1.0, ll) * jbm::log(xi1 * xi2 * xi3 * xi4) * sb * temp;  // ll = 1 .. 99
 }
 
 // Everett & Cashwell Planck sampler (planck.hpp:27-50); running sum of j^-4

@@ -485,6 +485,8 @@ __global__ void __launch_bounds__(256, 4) k_source_emit(StepParams P, int first_
   const unsigned warp0 = (unsigned)((blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5);
   const unsigned nwarps = (unsigned)(((long long)gridDim.x * blockDim.x) >> 5);
   const unsigned ncell_u = (unsigned)m.ncell, ncells_u = (unsigned)ncells;
+  const bool pow2 = (m.nxb[0] & (m.nxb[0] - 1)) == 0 && (m.nxb[1] & (m.nxb[1] - 1)) == 0;
+  const int sh1 = pow2 ? __ffs(m.nxb[0]) - 1 : -1, sh2 = pow2 ? __ffs(m.nxb[1]) - 1 : 0;
   unsigned long long my_n = 0;
   double my_e = 0.0;
   for (unsigned q = warp0; q < ncells_u; q += nwarps) {
@@ -507,7 +509,16 @@ __global__ void __launch_bounds__(256, 4) k_source_emit(StepParams P, int first_
     }
     if (npart == 0) continue;
     const DBlock &b = m.blocks[m.local_gid[lb]];
-    const int i = ci % m.nxb[0], j = (ci / m.nxb[0]) % m.nxb[1], k = ci / (m.nxb[0] * m.nxb[1]);
+    int i, j, k;
+    if (sh1 >= 0) {  // power-of-two block: shifts instead of three integer divisions per cell
+      i = ci & (m.nxb[0] - 1);
+      j = (ci >> sh1) & (m.nxb[1] - 1);
+      k = ci >> (sh1 + sh2);
+    } else {
+      i = ci % m.nxb[0];
+      j = (ci / m.nxb[0]) % m.nxb[1];
+      k = ci / (m.nxb[0] * m.nxb[1]);
+    }
     const double xi = cell_center(b, m.ng[0], 0, i), yi = cell_center(b, m.ng[1], 1, j),
                  zi = cell_center(b, m.ng[2], 2, k);
     const double temp = eos_temperature(P.cl, P.f.sie[c]);

@@ -27,6 +27,10 @@
 
 // deferred-work modes (low 3 bits of HPool::mode; bits 3-4 = axis, bit 5 = upper face)
 enum { HM_SCAT = 0, HM_LEAK = 1, HM_REJECT = 2, HM_CENSUS = 3, HM_EXIT = 4 };
+// census resamplings wait in a state of their own: they are half of a DDMC run's deferred work and take one draw
+// pair and an Xtoijk more than the others, so serving the two kinds in separate rounds keeps both full width
+// (mixed: 19 of 32 lanes, profiles/r02_v12_ncu_transport_hpool_cells64.md)
+enum { PS_PEND2 = 5 };
 
 template <int S>
 struct __align__(16) HPool {
@@ -192,10 +196,11 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
     const int s0 = W.st[lane], s1 = W.st[lane + 32u];
     const unsigned r0 = __ballot_sync(FULL, s0 == PS_READY), r1 = __ballot_sync(FULL, s1 == PS_READY);
     const unsigned q0 = __ballot_sync(FULL, s0 == PS_PEND), q1 = __ballot_sync(FULL, s1 == PS_PEND);
+    const unsigned z0 = __ballot_sync(FULL, s0 == PS_PEND2), z1 = __ballot_sync(FULL, s1 == PS_PEND2);
     const unsigned f0 = __ballot_sync(FULL, s0 == PS_FREE), f1 = __ballot_sync(FULL, s1 == PS_FREE);
     const unsigned w0 = __ballot_sync(FULL, s0 == PS_CENSUS || s0 == PS_ABS);
     const unsigned w1 = __ballot_sync(FULL, s1 == PS_CENSUS || s1 == PS_ABS);
-    const int n_ready = __popc(r0) + __popc(r1), n_pend = __popc(q0) + __popc(q1);
+    const int n_ready = __popc(r0) + __popc(r1), n_pend = __popc(q0) + __popc(q1), n_pend2 = __popc(z0) + __popc(z1);
     const int n_ret = __popc(w0) + __popc(w1), n_nonlive = n_ret + __popc(f0) + __popc(f1);
     bool can_claim = !exhausted;  // (two write cursors: see k_transport_pool)
     if (cur >= end && can_claim) {
@@ -204,7 +209,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
       can_claim = !__any_sync(FULL, old0 || old1);
     }
     const bool input_left = cur < end || can_claim;
-    const bool idle = n_ready + n_pend == 0;
+    const bool idle = n_ready + n_pend + n_pend2 == 0;
 
     // =====================================================================================
     // retire + refill
@@ -247,13 +252,8 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
       if (input_left) {
         if (cur >= end) {
           unsigned long long c0 = 0;
-          unsigned piece = IMC_CHUNK;  // guided claim, see k_transport_pool
-          if (lane == 0) {
-            const long long seen = (long long)*(volatile unsigned long long *)P.work;
-            const long long left = n - seen, share = left / (2ll * (long long)gridDim.x * POOL_WARPS);
-            if (share < IMC_CHUNK) piece = share < 64 ? 64u : ((unsigned)share & ~31u);
-            c0 = atomicAdd(P.work, (unsigned long long)piece);
-          }
+          unsigned piece = IMC_CHUNK;  // guided claim, see pool_claim
+          if (lane == 0) c0 = pool_claim(P.work, n, (long long)gridDim.x * POOL_WARPS, false, piece);
           c0 = __shfl_sync(FULL, c0, 0);
           piece = __shfl_sync(FULL, piece, 0);
           if ((long long)c0 >= n) {
@@ -326,9 +326,10 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
     // and albedo rejection (cosine law about the face normal, transport_utils.hpp:26-39), DDMC census
     // resampling (x, y drawn first; transport_utils.hpp:264-276) — and photons that left their meshblock
     // =====================================================================================
-    if (n_pend >= 32 || (n_pend > 0 && n_ready < ready_low)) {
+    if (n_pend >= 32 || n_pend2 >= 32 || (n_pend + n_pend2 > 0 && n_ready < ready_low)) {
       int cnt;
-      const int s = pool_pick(W.list, q0, q1, false, lane, lt, cnt);
+      const bool census_round = n_pend2 >= n_pend;  // the fuller of the two kinds
+      const int s = pool_pick(W.list, census_round ? z0 : q0, census_round ? z1 : q1, false, lane, lt, cnt);
       if (s >= 0) {
         const int md = W.mode[s];
         int mode = md & 7;
@@ -553,7 +554,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
             newst = PS_PEND;
             md = HM_LEAK | (face >> 1) << 3 | (face & 1) << 5;
           } else if (outcome == 3) {
-            newst = PS_PEND;
+            newst = PS_PEND2;
             md = HM_CENSUS;
           }
         }
@@ -606,7 +607,7 @@ struct HPoolTuning {
   int ctas;        // resident CTAs per SM the kernel is compiled for (registers: 65536 / (128 * ctas))
   int refill_min, ready_low;
 };
-static HPoolTuning g_hpool = {0, 24, 32};
+static HPoolTuning g_hpool = {0, 24, 16};  // measured: profiles/r02_hpool_first_ab_cells128.md
 
 template <int NDIM, int MINB, int S>
 static void launch_transport_hpool_b(const StepParams &P, long long first, long long n, double t_start, double dt,
@@ -645,13 +646,13 @@ static bool launch_transport_hpool(const StepParams &P, long long first, long lo
   if (n >= 0xffffffffLL || P.mesh.nxb[0] > 1022 || P.mesh.nxb[1] > 1022 || P.mesh.nxb[2] > 1022 || P.log.cap > 0) return false;
   if (g_hpool.ctas == 0) {
     const char *v = getenv("JB_HPOOL_CTAS");
-    g_hpool.ctas = v ? atoi(v) : 6;
+    g_hpool.ctas = v ? atoi(v) : 5;
     if (const char *r = getenv("JB_HPOOL_REFILL_MIN")) g_hpool.refill_min = max(1, min(atoi(r), 32));
     if (const char *r = getenv("JB_HPOOL_READY_LOW")) g_hpool.ready_low = max(1, min(atoi(r), 32));
   }
   switch (g_hpool.ctas) {
-    case 5: launch_transport_hpool_b<NDIM, 5, 64>(P, first, n, t_start, dt, st); break;
-    default: launch_transport_hpool_b<NDIM, 6, 64>(P, first, n, t_start, dt, st); break;
+    case 6: launch_transport_hpool_b<NDIM, 6, 64>(P, first, n, t_start, dt, st); break;
+    default: launch_transport_hpool_b<NDIM, 5, 64>(P, first, n, t_start, dt, st); break;
   }
   return true;
 }

@@ -74,6 +74,26 @@ __device__ __forceinline__ int pool_pick(unsigned char *list, const unsigned m0,
   return s;
 }
 
+// Guided claim of the next piece of the slot range: IMC_CHUNK slots while plenty remain, smaller pieces towards the
+// end (a piece = what is left / twice the warps, at least 64, a multiple of 32), so that the last warps finish
+// together — a short range (the arrivals of a later exchange iteration, a rank's 1/8 of the pool) otherwise ran on a
+// few warps with 1024 photons each (profiles/r02_v12_bench_cells256_gpus8_*.json: iterations 3+ of a cycle). The
+// look at the counter is only a hint; the atomic add is the claim. Out of line: once per ~1000 photons, and its
+// 64-bit division must not cost the transport loop registers. `fixed` (JB_POOL_FIXED_CHUNK) keeps IMC_CHUNK for A/B.
+__device__ __noinline__ unsigned long long pool_claim(unsigned long long *work, long long n, long long nwarps, bool fixed,
+                                                      unsigned &piece) {
+  piece = IMC_CHUNK;
+  if (!fixed) {
+    const long long seen = (long long)*(volatile unsigned long long *)work;
+    const long long left = n - seen;
+    if (left < 2ll * nwarps * IMC_CHUNK) {
+      const long long share = left / (2ll * nwarps);
+      piece = share < 64 ? 64u : ((unsigned)share & ~31u);
+    }
+  }
+  return atomicAdd(work, (unsigned long long)piece);
+}
+
 template <int NDIM, int MINB, bool VALIDATE, int ABS, int S>
 __global__ void __launch_bounds__(POOL_TPB, MINB)
     k_transport_pool(StepParams P, long long first, long long n, double t_start, double dt, int refill_min,
@@ -175,20 +195,10 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
       unsigned my32 = 0;
       if (input_left) {
         if (cur >= end) {
-          // guided claim: IMC_CHUNK slots while plenty remain, smaller pieces towards the end of the range (a
-          // piece = what is left / twice the warps, at least 64), so that the last warps finish together — a short
-          // range (the arrivals of a later exchange iteration, a rank's 1/8 of the pool) otherwise ran on a few
-          // warps with 1024 photons each (profiles/r02_v12_bench_cells256_gpus8_*.json: iterations 3+ of a cycle).
-          // The look at the counter is only a hint; the atomic add is the claim.
+          // guided claim (pool_claim): IMC_CHUNK slots while plenty remain, smaller pieces towards the end of the range
           unsigned long long c0 = 0;
           unsigned piece = IMC_CHUNK;
-          if (lane == 0) {
-            const long long seen = (long long)*(volatile unsigned long long *)P.work;
-            const long long left = n - seen, share = left / (2ll * (long long)gridDim.x * POOL_WARPS);
-            if (share < IMC_CHUNK && !(l2_prefetch & 2))  // (bit 1: fixed pieces, JB_POOL_FIXED_CHUNK, for A/B runs)
-              piece = share < 64 ? 64u : ((unsigned)share & ~31u);
-            c0 = atomicAdd(P.work, (unsigned long long)piece);
-          }
+          if (lane == 0) c0 = pool_claim(P.work, n, (long long)gridDim.x * POOL_WARPS, (l2_prefetch & 2) != 0, piece);
           c0 = __shfl_sync(FULL, c0, 0);
           piece = __shfl_sync(FULL, piece, 0);
           if ((long long)c0 >= n) {
