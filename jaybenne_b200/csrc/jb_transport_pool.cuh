@@ -498,7 +498,7 @@ static PoolTuning g_pool = {64, 24, 32, 0};
 void set_pool_prefetch(int on) { g_pool.l2_prefetch = (g_pool.l2_prefetch & ~1) | (on ? 1 : 0); }
 void set_pool_fixed_chunk(int on) { g_pool.l2_prefetch = (g_pool.l2_prefetch & ~2) | (on ? 2 : 0); }
 void set_pool_tuning(int slots, int refill_min, int ready_low) {
-  g_pool.slots = slots == 64 ? 64 : 56;
+  g_pool.slots = (slots == 64 || slots == 48 || slots == 664) ? slots : 56;  // 664: 64 slots at 6 CTAs per SM (experiment)
   g_pool.refill_min = max(1, min(refill_min, 32));
   g_pool.ready_low = max(1, min(ready_low, 32));
 }
@@ -519,16 +519,19 @@ static void launch_transport_pool_abs(const StepParams &P, long long first, long
   if (blocks > need) blocks = need;
   if (blocks < 1) blocks = 1;
   const int rf = g_pool.refill_min, rl = g_pool.ready_low, pf = g_pool.l2_prefetch;
-  // MINB CTAs x 4 pools fill most of the SM's shared memory: ask for the largest carve-out once
+  // MINB CTAs x 4 pools: ask for the shared-memory carve-out they need (and no more: the rest is L1)
   static bool carved = false;
   if (!carved) {
     carved = true;
+    const long long per_cta = (long long)sizeof(WarpPool<S, 2>) * POOL_WARPS + 16 + 1024;  // + the driver's 1 KB per CTA
+    int pct = (int)((per_cta * MINB * 100 + 233471) / 233472);
+    if (pct > 100) pct = 100;
     cudaFuncSetAttribute(k_transport_pool<NDIM, MINB, VALIDATE, ABS_GENERIC, S>,
-                         cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+                         cudaFuncAttributePreferredSharedMemoryCarveout, pct);
     cudaFuncSetAttribute(k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_DIRECT, S>,
-                         cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+                         cudaFuncAttributePreferredSharedMemoryCarveout, pct);
     cudaFuncSetAttribute(k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_KIRCHHOFF, S>,
-                         cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+                         cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   }
   if (P.cl.opacity_model != JB_OPAC_GRAY)
     k_transport_pool<NDIM, MINB, VALIDATE, ABS_GENERIC, S><<<(unsigned)blocks, POOL_TPB, 0, st>>>(P, first, n, t_start, dt, rf, rl, pf);
@@ -546,6 +549,10 @@ static bool launch_transport_pool(const StepParams &P, long long first, long lon
     launch_transport_pool_abs<NDIM, 4, true, 56>(P, first, n, t_start, dt, st);
   else if (g_pool.slots == 64)
     launch_transport_pool_abs<NDIM, 7, false, 64>(P, first, n, t_start, dt, st);
+  else if (g_pool.slots == 48 && NDIM == 3)
+    launch_transport_pool_abs<3, 7, false, 48>(P, first, n, t_start, dt, st);
+  else if (g_pool.slots == 664 && NDIM == 3)
+    launch_transport_pool_abs<3, 6, false, 64>(P, first, n, t_start, dt, st);
   else
     launch_transport_pool_abs<NDIM, 8, false, 56>(P, first, n, t_start, dt, st);
   return true;
