@@ -55,13 +55,29 @@ struct __align__(16) WarpPool {
   int2 blk[S];       // (local block, gid)
   unsigned idx[S];   // swarm slot the photon was loaded from, relative to `first` (tells its chunk)
   int cell[S];       // ip | jp << 10 | kp << 20 (interior indices)
-  unsigned char st[64];
-  unsigned char list[64];
+  unsigned char st[S > 64 ? 96 : 64];
+  unsigned char list[S > 64 ? 96 : 64];
 };
 
 // The lanes take the first 32 slots of the set (m0: slots 0-31, m1: slots 32-63), word m1 first when
 // `flip` (alternating the order keeps every slot from waiting more than one round). Returns the lane's
 // slot or -1; cnt = number of lanes served.
+// Three mask words (pools of up to 96 slots): the word order rotates with `rot` (0: 0 1 2, 1: 1 2 0, 2: 2 0 1).
+__device__ __forceinline__ int pool_pick3(unsigned char *list, const unsigned m0, const unsigned m1, const unsigned m2,
+                                          const unsigned rot, const unsigned lane, const unsigned lt, int &cnt) {
+  const int c0 = __popc(m0), c1 = __popc(m1), c2 = __popc(m2);
+  const int o0 = rot == 0 ? 0 : (rot == 1 ? c1 + c2 : c2);
+  const int o1 = rot == 0 ? c0 : (rot == 1 ? 0 : c2 + c0);
+  const int o2 = rot == 0 ? c0 + c1 : (rot == 1 ? c1 : 0);
+  if ((m0 >> lane) & 1u) list[__popc(m0 & lt) + o0] = (unsigned char)lane;
+  if ((m1 >> lane) & 1u) list[__popc(m1 & lt) + o1] = (unsigned char)(lane + 32u);
+  if ((m2 >> lane) & 1u) list[__popc(m2 & lt) + o2] = (unsigned char)(lane + 64u);
+  __syncwarp();
+  cnt = min(c0 + c1 + c2, 32);
+  const int s = (int)lane < cnt ? (int)list[lane] : -1;
+  __syncwarp();
+  return s;
+}
 __device__ __forceinline__ int pool_pick(unsigned char *list, const unsigned m0, const unsigned m1, const bool flip,
                                          const unsigned lane, const unsigned lt, int &cnt) {
   const int c0 = __popc(m0), c1 = __popc(m1);
@@ -94,13 +110,15 @@ __device__ __noinline__ unsigned long long pool_claim(unsigned long long *work, 
   return atomicAdd(work, (unsigned long long)piece);
 }
 
-template <int NDIM, int MINB, bool VALIDATE, int ABS, int S>
-__global__ void __launch_bounds__(POOL_TPB, MINB)
+template <int NDIM, int MINB, bool VALIDATE, int ABS, int S, int WARPS = POOL_WARPS>
+__global__ void __launch_bounds__(WARPS * 32, MINB)
     k_transport_pool(StepParams P, long long first, long long n, double t_start, double dt, int refill_min,
                      int ready_low, int l2_prefetch) {
   constexpr int NQ = ABS == ABS_GRAY_DIRECT ? 1 : 2;
-  static_assert(S > 32 && S <= 64, "two slots per lane");
-  __shared__ WarpPool<S, NQ> pools[POOL_WARPS];
+  static_assert(S > 32 && S <= 96, "two or three slots per lane");
+  constexpr bool W3 = S > 64;  // three mask words
+  constexpr unsigned NW = W3 ? 3u : 2u;
+  __shared__ WarpPool<S, NQ> pools[WARPS];
   __shared__ unsigned sh_cnt[4];  // crossings, removed in the segment phase (escaped / sent / lost)
 
   const DMesh &m = P.mesh;
@@ -121,6 +139,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
 
   W.st[lane] = PS_FREE;
   W.st[lane + 32u] = (lane + 32u < (unsigned)S) ? PS_FREE : PS_NONE;
+  if (W3) W.st[lane + 64u] = (lane + 64u < (unsigned)S) ? PS_FREE : PS_NONE;
   if (threadIdx.x < 4) sh_cnt[threadIdx.x] = 0u;
   __syncthreads();
 
@@ -130,20 +149,23 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
   unsigned c_base = 0, wr = 0;  // current chunk: first slot and write cursor (wr <= cur: only slots already read)
   unsigned p_wr = 0;            // write cursor of the previous chunk (all of its slots have been read)
   bool exhausted = false;
-  bool flip = false;
+  unsigned rot = 0;  // which mask word the segment phase serves first
   unsigned c_seg = 0, c_scat = 0, c_abs = 0, bad = 0;
   double e_abs = 0.0;
 
   for (;;) {
     __syncwarp();
-    const int s0 = W.st[lane], s1 = W.st[lane + 32u];
+    const int s0 = W.st[lane], s1 = W.st[lane + 32u], s2 = W3 ? (int)W.st[lane + 64u] : (int)PS_NONE;
     const unsigned r0 = __ballot_sync(FULL, s0 == PS_READY), r1 = __ballot_sync(FULL, s1 == PS_READY);
     const unsigned q0 = __ballot_sync(FULL, s0 == PS_PEND), q1 = __ballot_sync(FULL, s1 == PS_PEND);
     const unsigned f0 = __ballot_sync(FULL, s0 == PS_FREE), f1 = __ballot_sync(FULL, s1 == PS_FREE);
     const unsigned w0 = __ballot_sync(FULL, s0 == PS_CENSUS || s0 == PS_ABS);
     const unsigned w1 = __ballot_sync(FULL, s1 == PS_CENSUS || s1 == PS_ABS);
-    const int n_ready = __popc(r0) + __popc(r1), n_pend = __popc(q0) + __popc(q1);
-    const int n_ret = __popc(w0) + __popc(w1), n_nonlive = n_ret + __popc(f0) + __popc(f1);
+    const unsigned r2 = W3 ? __ballot_sync(FULL, s2 == PS_READY) : 0u, q2 = W3 ? __ballot_sync(FULL, s2 == PS_PEND) : 0u;
+    const unsigned f2 = W3 ? __ballot_sync(FULL, s2 == PS_FREE) : 0u;
+    const unsigned w2 = W3 ? __ballot_sync(FULL, s2 == PS_CENSUS || s2 == PS_ABS) : 0u;
+    const int n_ready = __popc(r0) + __popc(r1) + __popc(r2), n_pend = __popc(q0) + __popc(q1) + __popc(q2);
+    const int n_ret = __popc(w0) + __popc(w1) + __popc(w2), n_nonlive = n_ret + __popc(f0) + __popc(f1) + __popc(f2);
     // two write cursors are kept, so the next chunk is claimed only once the chunk BEFORE the current one has
     // no photon left in the pool (a chunk is >= 16 refills long: by then they have all retired, except in
     // media where single histories run to hundreds of segments)
@@ -151,7 +173,8 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
     if (cur >= end && can_claim) {
       const bool old0 = s0 != PS_FREE && W.idx[lane] < c_base;
       const bool old1 = s1 != PS_FREE && s1 != PS_NONE && W.idx[lane + 32u] < c_base;
-      can_claim = !__any_sync(FULL, old0 || old1);
+      const bool old2 = W3 && s2 != PS_FREE && s2 != PS_NONE && W.idx[W3 ? lane + 64u : lane] < c_base;
+      can_claim = !__any_sync(FULL, old0 || old1 || old2);
     }
     const bool input_left = cur < end || can_claim;
     const bool idle = n_ready + n_pend == 0;
@@ -161,7 +184,8 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
     // =====================================================================================
     if ((n_nonlive >= refill_min || idle) && (input_left || n_ret > 0)) {
       int cnt;
-      const int s = pool_pick(W.list, input_left ? (w0 | f0) : w0, input_left ? (w1 | f1) : w1, false, lane, lt, cnt);
+      const int s = pool_pick3(W.list, input_left ? (w0 | f0) : w0, input_left ? (w1 | f1) : w1,
+                               input_left ? (w2 | f2) : w2, 0u, lane, lt, cnt);
       {
         const int old = s >= 0 ? (int)W.st[s] : PS_FREE;
         // the photon reached t_end (the reference's loop leaves it in place): back to the swarm arrays, packed
@@ -198,7 +222,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
           // guided claim (pool_claim): IMC_CHUNK slots while plenty remain, smaller pieces towards the end of the range
           unsigned long long c0 = 0;
           unsigned piece = IMC_CHUNK;
-          if (lane == 0) c0 = pool_claim(P.work, n, (long long)gridDim.x * POOL_WARPS, (l2_prefetch & 2) != 0, piece);
+          if (lane == 0) c0 = pool_claim(P.work, n, (long long)gridDim.x * WARPS, (l2_prefetch & 2) != 0, piece);
           c0 = __shfl_sync(FULL, c0, 0);
           piece = __shfl_sync(FULL, piece, 0);
           if ((long long)c0 >= n) {
@@ -296,7 +320,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
     // =====================================================================================
     if (n_pend >= 32 || (n_pend > 0 && n_ready < ready_low)) {
       int cnt;
-      const int s = pool_pick(W.list, q0, q1, false, lane, lt, cnt);
+      const int s = pool_pick3(W.list, q0, q1, q2, 0u, lane, lt, cnt);
       if (s >= 0) {
         Rng2 rng;
         const uint2 ia = W.ida[s], ib = W.idb[s], cy = W.carry[s];
@@ -316,9 +340,9 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
     // =====================================================================================
     // segment: one iteration of the while (t < t_end) loop, transport.cpp:112-171
     // =====================================================================================
-    flip = !flip;
+    rot = rot + 1u == NW ? 0u : rot + 1u;
     int cnt;
-    const int s = pool_pick(W.list, r0, r1, flip, lane, lt, cnt);
+    const int s = pool_pick3(W.list, r0, r1, r2, rot, lane, lt, cnt);
     if (s >= 0) {
       c_seg++;
       Photon p;
@@ -489,7 +513,7 @@ __global__ void __launch_bounds__(POOL_TPB, MINB)
 }
 
 struct PoolTuning {
-  int slots;        // 56 (8 CTAs of 4 warps per SM) or 64 (7 CTAs)
+  int slots;        // see set_pool_tuning
   int refill_min;   // retire + refill when this many slots of a warp hold no live photon
   int ready_low;    // scatter early when fewer READY photons than this remain
   int l2_prefetch;  // 1: cp.async.bulk.prefetch.L2 of the next refill window (JB_POOL_PREFETCH; measured)
@@ -498,12 +522,15 @@ static PoolTuning g_pool = {64, 24, 32, 0};
 void set_pool_prefetch(int on) { g_pool.l2_prefetch = (g_pool.l2_prefetch & ~1) | (on ? 1 : 0); }
 void set_pool_fixed_chunk(int on) { g_pool.l2_prefetch = (g_pool.l2_prefetch & ~2) | (on ? 2 : 0); }
 void set_pool_tuning(int slots, int refill_min, int ready_low) {
-  g_pool.slots = (slots == 64 || slots == 48 || slots == 664) ? slots : 56;  // 664: 64 slots at 6 CTAs per SM (experiment)
+  // 64 (shipped): 64 slots, 5 CTAs of 4 warps per SM = 96 registers, no spills. A/B configurations
+  // (profiles/r02_v10_tuning_cells256.md): 764 / 664 = 64 slots at 7 / 6 CTAs (72 / 80 registers, spills),
+  // 588 = 88 slots (three per lane) at 5 CTAs, 56 = 56 slots at 8 CTAs (64 registers)
+  g_pool.slots = (slots == 64 || slots == 664 || slots == 764 || slots == 588) ? slots : 56;
   g_pool.refill_min = max(1, min(refill_min, 32));
   g_pool.ready_low = max(1, min(ready_low, 32));
 }
 
-template <int NDIM, int MINB, bool VALIDATE, int S>
+template <int NDIM, int MINB, bool VALIDATE, int S, int WARPS = POOL_WARPS>
 static void launch_transport_pool_abs(const StepParams &P, long long first, long long n, double t_start, double dt,
                                       cudaStream_t st) {
   static int n_sm = 0;
@@ -515,7 +542,7 @@ static void launch_transport_pool_abs(const StepParams &P, long long first, long
   }
   // persistent grid: MINB CTAs on each SM; a short range gets one warp per S photons
   long long blocks = (long long)n_sm * MINB;
-  const long long need = (n + (long long)POOL_WARPS * S - 1) / ((long long)POOL_WARPS * S);
+  const long long need = (n + (long long)WARPS * S - 1) / ((long long)WARPS * S);
   if (blocks > need) blocks = need;
   if (blocks < 1) blocks = 1;
   const int rf = g_pool.refill_min, rl = g_pool.ready_low, pf = g_pool.l2_prefetch;
@@ -523,22 +550,22 @@ static void launch_transport_pool_abs(const StepParams &P, long long first, long
   static bool carved = false;
   if (!carved) {
     carved = true;
-    const long long per_cta = (long long)sizeof(WarpPool<S, 2>) * POOL_WARPS + 16 + 1024;  // + the driver's 1 KB per CTA
+    const long long per_cta = (long long)sizeof(WarpPool<S, 2>) * WARPS + 16 + 1024;  // + the driver's 1 KB per CTA
     int pct = (int)((per_cta * MINB * 100 + 233471) / 233472);
     if (pct > 100) pct = 100;
-    cudaFuncSetAttribute(k_transport_pool<NDIM, MINB, VALIDATE, ABS_GENERIC, S>,
+    cudaFuncSetAttribute(k_transport_pool<NDIM, MINB, VALIDATE, ABS_GENERIC, S, WARPS>,
                          cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-    cudaFuncSetAttribute(k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_DIRECT, S>,
+    cudaFuncSetAttribute(k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_DIRECT, S, WARPS>,
                          cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-    cudaFuncSetAttribute(k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_KIRCHHOFF, S>,
+    cudaFuncSetAttribute(k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_KIRCHHOFF, S, WARPS>,
                          cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   }
   if (P.cl.opacity_model != JB_OPAC_GRAY)
-    k_transport_pool<NDIM, MINB, VALIDATE, ABS_GENERIC, S><<<(unsigned)blocks, POOL_TPB, 0, st>>>(P, first, n, t_start, dt, rf, rl, pf);
+    k_transport_pool<NDIM, MINB, VALIDATE, ABS_GENERIC, S, WARPS><<<(unsigned)blocks, WARPS * 32, 0, st>>>(P, first, n, t_start, dt, rf, rl, pf);
   else if (P.cl.gray_mode == JB_GRAY_DIRECT)
-    k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_DIRECT, S><<<(unsigned)blocks, POOL_TPB, 0, st>>>(P, first, n, t_start, dt, rf, rl, pf);
+    k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_DIRECT, S, WARPS><<<(unsigned)blocks, WARPS * 32, 0, st>>>(P, first, n, t_start, dt, rf, rl, pf);
   else
-    k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_KIRCHHOFF, S><<<(unsigned)blocks, POOL_TPB, 0, st>>>(P, first, n, t_start, dt, rf, rl, pf);
+    k_transport_pool<NDIM, MINB, VALIDATE, ABS_GRAY_KIRCHHOFF, S, WARPS><<<(unsigned)blocks, WARPS * 32, 0, st>>>(P, first, n, t_start, dt, rf, rl, pf);
 }
 // false: the range or the mesh does not fit the kernel's packed indices -> the caller takes k_transport_imc
 template <int NDIM>
@@ -548,11 +575,13 @@ static bool launch_transport_pool(const StepParams &P, long long first, long lon
   if (g_tuning.validate)
     launch_transport_pool_abs<NDIM, 4, true, 56>(P, first, n, t_start, dt, st);
   else if (g_pool.slots == 64)
-    launch_transport_pool_abs<NDIM, 7, false, 64>(P, first, n, t_start, dt, st);
-  else if (g_pool.slots == 48 && NDIM == 3)
-    launch_transport_pool_abs<3, 7, false, 48>(P, first, n, t_start, dt, st);
+    launch_transport_pool_abs<NDIM, 5, false, 64>(P, first, n, t_start, dt, st);
+  else if (g_pool.slots == 764 && NDIM == 3)
+    launch_transport_pool_abs<3, 7, false, 64>(P, first, n, t_start, dt, st);
   else if (g_pool.slots == 664 && NDIM == 3)
     launch_transport_pool_abs<3, 6, false, 64>(P, first, n, t_start, dt, st);
+  else if (g_pool.slots == 588 && NDIM == 3)
+    launch_transport_pool_abs<3, 5, false, 88>(P, first, n, t_start, dt, st);
   else
     launch_transport_pool_abs<NDIM, 8, false, 56>(P, first, n, t_start, dt, st);
   return true;
