@@ -26,7 +26,10 @@ inside jb_radiation_step.
           per photon), against a DFMA-chain peak measured in the same run.
   variants  timed in the same run, each a few seconds: `continuing` (8 consecutive cycles of one
           simulation), `continuing_sorted` (same, pool re-sorted by cell every cycle), `ddmc`
-          (128^3 optically thick, k_transport_hybrid) and `stream` (free streaming).
+          (128^3 optically thick, k_transport_hpool) and `stream` (free streaming).
+  timeline  device-timed phases of the last timed step (jb_step_timeline): rank 0's list, the sums
+          per phase as max / min over the ranks, and which swarm exchange ran (direct peer
+          stores over NVLink, or NCCL send / recv per iteration).
   cpu_baseline  the CPU oracle (reference per-particle headers, OpenMP over the photons of
           all blocks, the reference's XorShift64 pool with one state per thread) on a
           64^3-cell twin of the same workload on the box's host cores (rank 0, N = 1 only).
@@ -484,7 +487,8 @@ def main():
     plain = not (args.stream or args.ddmc)
     if args.variants and plain:
         variants["continuing"] = variant("continuing", lambda: dict(
-            continuing_run(W, 8), workload=f"{cells}^3: thermal initialisation + 8 consecutive cycles, unsorted pool"))
+            continuing_run(W, 8), workload=f"{cells}^3: thermal initialisation + 8 consecutive cycles; the pool stays ordered "
+                                             "(chunk-local write-back, order-preserving squeeze), no sort"))
         if args.sort_interval == 0:
             def sorted_run():
                 Ws = W
@@ -531,7 +535,7 @@ def main():
                     Wv.close()
             return run
         variants["ddmc"] = variant("ddmc", small(False, True, min(cells, 128),
-                                   "C5-ddmc {cells}^3 / {photons} photons: sigma*dx = 8, use_ddmc, tau_ddmc = 5 (k_transport_hybrid)"))
+                                   "C5-ddmc {cells}^3 / {photons} photons: sigma*dx = 8, use_ddmc, tau_ddmc = 5 (k_transport_hpool)"))
         variants["stream"] = variant("stream", small(True, False, cells,
                                      "C5-stream {cells}^3 / {photons} photons: dt = dx/(2c), kappa = sigma = 0 (bandwidth-bound limit)"))
 
@@ -552,7 +556,7 @@ def main():
                     "kernel": tj.get("kernel")}
     fps = float(tj.get("fp64_flops_per_segment", 324.0)) if tj else 324.0
     spp = seg / max(args.steps * (last["n_start"] + last["n_sourced"]), 1)
-    kernel_name = "k_transport_hybrid" if args.ddmc else os.environ.get("JB_TRANSPORT_VARIANT", "2") == "1" and "k_transport_imc" or "k_transport_pool"
+    kernel_name = (os.environ.get("JB_TRANSPORT_VARIANT", "2") == "2" and "k_transport_hpool" or "k_transport_hybrid") if args.ddmc else os.environ.get("JB_TRANSPORT_VARIANT", "2") == "1" and "k_transport_imc" or "k_transport_pool"
     roofline = {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "ncu": ncu_pipe,
                 "note": f"{spp:.1f} segments per photon make this kernel FP64-issue / latency bound ({fps:.0f} FP64 flop per "

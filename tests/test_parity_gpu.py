@@ -365,6 +365,22 @@ def test_pool_stays_ordered_through_transport_and_squeeze():
     pu.assert_swarm_equal(gpu.jb, ora.jb)
 
 
+def test_step_timeline_reports_the_phases_of_the_last_step():
+    """jb_step_timeline: device-timed phases of the last RadiationStep in stream order; one transport phase on a
+    single rank, every duration >= 0, and together no longer than the step's own event bracket."""
+    gpu, _ = pu.make_pair(text=pu.synthetic_text(n=16, nb=8, num_particles=20000))
+    gpu.ProblemGenerator(pu.synthetic_density)
+    st = gpu.Step()
+    tl = gpu.jb.step_timeline()
+    names = [n for n, _ in tl]
+    assert names.count("transport") == 1 and "exchange" not in names
+    assert names[0] == "fields" and names[-1] == "end" and "tally" in names and "source" in names
+    assert all(ms >= 0.0 for _, ms in tl)
+    assert sum(ms for _, ms in tl) <= st["ms_total"] * 1.001 + 0.01
+    assert abs(dict(tl)["transport"] - st["ms_transport"]) <= 0.05 + 0.05 * st["ms_transport"]
+    assert gpu.jb.exchange_mode() == 0
+
+
 def test_range_test_free_division_is_the_ieee_quotient():
     """jbm::div_normal (nvcc's fast-path sequence without the operand test and slow-path call) must return the
     correctly rounded quotient, i.e. the bits of `/`, over the operand ranges the kernels use it on."""
