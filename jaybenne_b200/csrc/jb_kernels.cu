@@ -1133,6 +1133,38 @@ __global__ void __launch_bounds__(256) k_tally(StepParams P, long long n, unsign
   warp_add_u64(n_alive, a);
   warp_add_energy(P, EB_CENSUS, e);
 }
+// EvaluateRadiationEnergy straight after a sourcing pass into an EMPTY pool: every photon of a cell carries that
+// cell's weight, so tally(cell) = sum over its src_num photons of src_ew / dV needs no pass over the swarm (the
+// same additions the photon loop makes, in photon order). One thread per cell; census totals ride along.
+__global__ void __launch_bounds__(256) k_tally_sourced(StepParams P, long long ncells, unsigned long long *n_alive) {
+  const DMesh &m = P.mesh;
+  unsigned long long a = 0;
+  double e = 0.0;
+  for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncells; c += (long long)gridDim.x * blockDim.x) {
+    const BlkGeo *geo = m.geo + __ldg(&m.local_gid[(int)(c / m.ncell)]);
+    const double dv = __ldg(&geo->xd[0]).y * __ldg(&geo->xd[1]).y * __ldg(&geo->xd[2]).y;
+    const int npart = (int)round(P.f.src_num[c]);
+    const double ew = P.f.src_ew[c];
+    double t = 0.0;
+    if (npart > 0) {
+      const double v = ew / dv;
+      for (int np = 0; np < npart; ++np) {
+        t += v;
+        e += ew;
+      }
+      a += (unsigned long long)npart;
+    }
+    P.f.tally[c] = t;
+  }
+  warp_add_u64(n_alive, a);
+  warp_add_energy(P, EB_CENSUS, e);
+}
+void launch_tally_sourced(const StepParams &P, unsigned long long *n_alive, double *e_sum, cudaStream_t st) {
+  const long long ncells = (long long)P.mesh.nlocal * P.mesh.ncell;
+  cudaMemsetAsync(P.ebins + EB_CENSUS * EBINS, 0, sizeof(double) * EBINS, st);
+  if (ncells > 0) k_tally_sourced<<<grid_for(ncells, 256), 256, 0, st>>>(P, ncells, n_alive);
+  launch_fold_bins(P, EB_CENSUS, e_sum, st);
+}
 void launch_tally(const StepParams &P, long long n, unsigned long long *n_alive, double *e_sum, cudaStream_t st) {
   const long long ncells = (long long)P.mesh.nlocal * P.mesh.ncell;
   cudaMemsetAsync(P.f.tally, 0, sizeof(double) * ncells, st);

@@ -659,14 +659,24 @@ jb_status jb_set_fields(jb_ctx *c, int32_t field, int32_t n, const int32_t *gids
   double *p = field_ptr(c, field, &nb);
   if (!p) return fail(c, JB_ERR_INVALID, "bad field (face probabilities exist only with use_ddmc)");
   JB_CUDA(c, cudaSetDevice(c->device));
-  for (int32_t q = 0; q < n; ++q) {
-    const int32_t gid = gids[q];
-    if (gid < 0 || gid >= c->mesh.nblocks || c->gid_to_local[gid] < 0 || !srcs[q]) {
-      cudaStreamSynchronize(c->stream);
+  for (int32_t q = 0; q < n; ++q)
+    if (gids[q] < 0 || gids[q] >= c->mesh.nblocks || c->gid_to_local[gids[q]] < 0 || !srcs[q])
       return fail(c, JB_ERR_INVALID, "block not local");
+  // Blocks that are neighbours both in the caller's memory and in the library's field array (a MeshData pack, a
+  // [block][cell] host array) travel as ONE copy: 512 blocks x 256 KB cost ~3 ms of cudaMemcpyAsync calls per field
+  // and direction otherwise. A merged copy that the runtime refuses (the run spans two host allocations) is
+  // repeated block by block.
+  for (int32_t q = 0; q < n;) {
+    int32_t e = q + 1;
+    while (e < n && c->gid_to_local[gids[e]] == c->gid_to_local[gids[e - 1]] + 1 && srcs[e] == srcs[e - 1] + nb) ++e;
+    double *dst = p + (size_t)c->gid_to_local[gids[q]] * nb;
+    if (cudaMemcpyAsync(dst, srcs[q], sizeof(double) * nb * (size_t)(e - q), cudaMemcpyDefault, c->stream) != cudaSuccess) {
+      cudaGetLastError();
+      for (int32_t r = q; r < e; ++r)
+        JB_CUDA(c, cudaMemcpyAsync(p + (size_t)c->gid_to_local[gids[r]] * nb, srcs[r], sizeof(double) * nb, cudaMemcpyDefault,
+                                   c->stream));
     }
-    JB_CUDA(c, cudaMemcpyAsync(p + (size_t)c->gid_to_local[gid] * nb, srcs[q], sizeof(double) * nb, cudaMemcpyDefault,
-                               c->stream));
+    q = e;
   }
   JB_CUDA(c, cudaStreamSynchronize(c->stream));
   c->props_dirty = true;
@@ -678,18 +688,24 @@ jb_status jb_get_fields(jb_ctx *c, int32_t field, int32_t n, const int32_t *gids
   long long nb;
   double *p = field_ptr(c, field, &nb);
   JB_CUDA(c, cudaSetDevice(c->device));
-  for (int32_t q = 0; q < n; ++q) {
-    const int32_t gid = gids[q];
-    if (gid < 0 || gid >= c->mesh.nblocks || c->gid_to_local[gid] < 0 || !dsts[q]) {
-      cudaStreamSynchronize(c->stream);
+  for (int32_t q = 0; q < n; ++q)
+    if (gids[q] < 0 || gids[q] >= c->mesh.nblocks || c->gid_to_local[gids[q]] < 0 || !dsts[q])
       return fail(c, JB_ERR_INVALID, "block not local");
+  if (!p) {
+    for (int32_t q = 0; q < n; ++q) memset(dsts[q], 0, sizeof(double) * nb);
+    return JB_OK;
+  }
+  for (int32_t q = 0; q < n;) {  // runs of neighbouring blocks as one copy, see jb_set_fields
+    int32_t e = q + 1;
+    while (e < n && c->gid_to_local[gids[e]] == c->gid_to_local[gids[e - 1]] + 1 && dsts[e] == dsts[e - 1] + nb) ++e;
+    const double *src = p + (size_t)c->gid_to_local[gids[q]] * nb;
+    if (cudaMemcpyAsync(dsts[q], src, sizeof(double) * nb * (size_t)(e - q), cudaMemcpyDefault, c->stream) != cudaSuccess) {
+      cudaGetLastError();
+      for (int32_t r = q; r < e; ++r)
+        JB_CUDA(c, cudaMemcpyAsync(dsts[r], p + (size_t)c->gid_to_local[gids[r]] * nb, sizeof(double) * nb, cudaMemcpyDefault,
+                                   c->stream));
     }
-    if (!p) {
-      memset(dsts[q], 0, sizeof(double) * nb);
-      continue;
-    }
-    JB_CUDA(c, cudaMemcpyAsync(dsts[q], p + (size_t)c->gid_to_local[gid] * nb, sizeof(double) * nb, cudaMemcpyDefault,
-                               c->stream));
+    q = e;
   }
   JB_CUDA(c, cudaStreamSynchronize(c->stream));
   return JB_OK;
@@ -1116,12 +1132,16 @@ jb_status jb_source_photons(jb_ctx *c, int32_t source_type, double t_start, doub
   return JB_OK;
 }
 
-jb_status jb_evaluate_radiation_energy(jb_ctx *c) {
-  JB_REQUIRE_MESH(c);
+// `from_source`: the pool holds exactly the photons of the sourcing pass that just ran over all local blocks
+// (jb_initialize_radiation into an empty pool) — the tally then comes from the per-cell source fields
+static jb_status evaluate_radiation_energy(jb_ctx *c, bool from_source) {
   StepParams P = make_params(c);
   JB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * 2, c->stream));
   JB_CUDA(c, cudaMemsetAsync(c->d_esum, 0, sizeof(double), c->stream));
-  launch_tally(P, c->n, c->d_counters, c->d_esum, c->stream);
+  if (from_source)
+    launch_tally_sourced(P, c->d_counters, c->d_esum, c->stream);
+  else
+    launch_tally(P, c->n, c->d_counters, c->d_esum, c->stream);
   c->launches += 1 + (c->n > 0);
   JB_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
   JB_CUDA(c, cudaMemcpyAsync(c->h_counters + 2, c->d_esum, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
@@ -1132,18 +1152,28 @@ jb_status jb_evaluate_radiation_energy(jb_ctx *c) {
   c->census_valid = true;
   return JB_OK;
 }
+jb_status jb_evaluate_radiation_energy(jb_ctx *c) {
+  JB_REQUIRE_MESH(c);
+  return evaluate_radiation_energy(c, false);
+}
 
 // InitializeRadiation on every local block (jaybenne.cpp:570-578). The reference sources
 // each block through its own MeshBlockData pack (nblocks = 1 in the per-cell count); the
 // blocks are independent, so one launch covers them all.
 jb_status jb_initialize_radiation(jb_ctx *c, int32_t is_thermal) {
   JB_REQUIRE_MESH(c);
+  const bool was_empty = c->n == 0 && c->n_holes == 0;
   if (is_thermal) {
     jb_status s = source_photons(c, 0, (int)c->local_gid.size(), JB_SOURCE_THERMAL, 0.0, 0.0, 1, c->source_call);
     if (s != JB_OK) return s;
     c->source_call++;
   }
-  jb_status s = jb_evaluate_radiation_energy(c);
+  static int fuse = -1;  // JB_TALLY_FROM_SOURCE=0: always walk the swarm (A/B, cross-check)
+  if (fuse < 0) {
+    const char *v = getenv("JB_TALLY_FROM_SOURCE");
+    fuse = v ? (atoi(v) != 0) : 1;
+  }
+  jb_status s = evaluate_radiation_energy(c, is_thermal && was_empty && fuse);
   if (s != JB_OK) return s;
   JB_CUDA(c, cudaStreamSynchronize(c->stream));
   return JB_OK;
