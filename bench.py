@@ -347,6 +347,10 @@ def main():
                 self.host_sie[q] = cv * self.mb.tt0
             self.dev_rho, self.dev_sie = self.host_rho.cuda(), self.host_sie.cuda()
             self.dt = self.mb.cfg.dt
+            # per-block addresses are constants of the workload: built once, not inside the timed steps
+            self.p = {k: self.ptrs(t) for k, t in (("dev_rho", self.dev_rho), ("dev_sie", self.dev_sie),
+                                                   ("host_rho", self.host_rho), ("host_sie", self.host_sie),
+                                                   ("host_tally", self.host_tally), ("host_u", self.host_u))}
 
         def ptrs(self, t):
             return [t[q].data_ptr() for q in range(len(self.gids))]
@@ -355,8 +359,8 @@ def main():
             jb = self.jb
             jb.clear_particles()
             jb.reset_streams()      # every step sees the same photons: the steps are identical batches
-            jb.set_fields_ptr("density", self.gids, self.ptrs(self.host_rho if host else self.dev_rho))
-            jb.set_fields_ptr("sie", self.gids, self.ptrs(self.host_sie if host else self.dev_sie))
+            jb.set_fields_ptr("density", self.gids, self.p["host_rho" if host else "dev_rho"])
+            jb.set_fields_ptr("sie", self.gids, self.p["host_sie" if host else "dev_sie"])
             jb.InitializeRadiation(True)
             jb.PostInitialization()
 
@@ -368,8 +372,8 @@ def main():
             return st
 
         def read_back(self):
-            self.jb.get_fields_ptr("energy_tally", self.gids, self.ptrs(self.host_tally))
-            self.jb.get_fields_ptr("internal_energy", self.gids, self.ptrs(self.host_u))
+            self.jb.get_fields_ptr("energy_tally", self.gids, self.p["host_tally"])
+            self.jb.get_fields_ptr("internal_energy", self.gids, self.p["host_u"])
 
         def timed(self, nsteps, host=False):
             """(segments of this rank, device ms, per-step stats)"""

@@ -210,6 +210,17 @@ def test_large_run_conservation_and_count_identities():
         assert abs(edelta - (st["e_absorbed"] - st["e_sourced"])) <= 1e-9 * st["e_absorbed"]
 
 
+def test_mid_size_run_is_bit_identical_to_the_oracle():
+    """32^3 cells in 16^3 blocks, 1e6 photons, two cycles with emission and feedback: the largest case the serial
+    oracle finishes in seconds (8e6 segments per cycle). Thousands of chunks per warp-private pool, every phase of
+    k_transport_pool at full width, block crossings in all 26 directions — counts, census swarm (positions,
+    directions, times, draw counters, cells) bit for bit, tallies to 1e-12."""
+    text = pu.synthetic_text(n=32, nb=16, num_particles=1000000)
+    gpu, ora = pu.make_pair(text=text)
+    sg, so = run_pair(gpu, ora, cycles=2, density_fn=pu.synthetic_density)
+    assert sg["n_segments"] > 4000000 and sg["n_block_crossings"] > 100000
+
+
 # ---- north_star check 3: seed ensembles against the reference-faithful generator ------------------
 def _ensemble(api, rng_mode, deck, overrides, cycles, seeds, ci=False):
     from jaybenne_b200 import Mcblock
