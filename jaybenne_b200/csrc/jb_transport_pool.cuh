@@ -13,7 +13,7 @@
 // 21.8 of 32 lanes wide — 41 % of the issued warp-instructions sat in side paths that a few lanes take
 // each iteration (the scatter's extra Philox block + sqrt + sincos at ~6 lanes, the refill at ~4, the
 // census write-back at ~3, the absorption deposit at ~2), while 228 KB of shared memory went unused.
-// Here the photon state lives in shared memory (S slots per warp, SoA, ~116 B per slot) and a slot is in
+// Here the photon state lives in shared memory (S slots per warp, SoA, 120 B per slot) and a slot is in
 // one of five states; the warp looks at the state counts and runs ONE phase per iteration:
 //   * retire + refill  (>= refill_min slots hold no live photon): absorbed photons deposit their energy,
 //     census photons are written back to the swarm arrays, and the freed slots take the next photons of
@@ -22,8 +22,11 @@
 //     scatter for up to 32 photons at once;
 //   * segment  (otherwise): up to 32 READY photons advance one iteration of the while (t < t_end) loop.
 // Only the block hand-over and the domain boundary conditions (1.5 % of the segments) stay inside the
-// segment phase. Registers hold a photon only for the duration of a phase, so the 148 B of spills of
-// v9 are gone with the per-lane state.
+// segment phase. Registers hold a photon only for the duration of a phase.
+//
+// v13 — registers before warps: 5 CTAs of 4 warps per SM (96 registers, no spills, ~95 KB of L1 beside 160 KB of
+// pools) beat 7 CTAs (72 registers, 140 B spilled, ~30 KB of L1) by 3.5 %: 7.6 instead of 10.6 cycles between a
+// warp's instructions (profiles/r02_v13_ncu_transport_pool_cells64.md, profiles/r02_v10_tuning_cells256.md).
 //
 // v12 — the pool stays ORDERED. A warp owns the 1024-slot chunks it claims, so it writes its census photons
 // back to the FRONT of their chunk, in the order they finish (the k-th photon to retire goes to chunk + k,
