@@ -242,6 +242,18 @@ class Package {
     return s;
   }
   int64_t KernelLaunches() const { return jb_kernel_launches(ctx_); }
+  // device-timed phases of the last RadiationStep in stream order: (JB_TL_* label, milliseconds)
+  std::vector<std::pair<int, float>> StepTimeline() const {
+    int32_t labels[96];
+    float ms[96];
+    int32_t n = 0;
+    check(jb_step_timeline(ctx_, labels, ms, 96, &n));
+    std::vector<std::pair<int, float>> out;
+    for (int32_t q = 0; q < n && q < 96; ++q) out.emplace_back((int)labels[q], ms[q]);
+    return out;
+  }
+  // 0 single rank, 1 NCCL send / recv per iteration, 2 direct peer stores over NVLink
+  int ExchangeMode() const { return (int)jb_exchange_mode(ctx_); }
 
   // the `photons` swarm of this rank as host SoA (jaybenne.cpp:236-245) for dumps / restart
   struct Photons {

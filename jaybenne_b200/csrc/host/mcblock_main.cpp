@@ -246,6 +246,8 @@ class Mcblock {
     while (time_ < tlim_ && (nlim_ < 0 || ncycle_ < nlim_)) {
       if (opt_.max_cycles >= 0 && ncycle_ >= opt_.max_cycles) break;
       const jb_cycle_stats s = Step();
+      for (const auto &ph : pkg_->StepTimeline())
+        if (ph.first >= 0 && ph.first < 9) phase_ms_[ph.first] += ph.second;
       hst << ncycle_ << ',' << time_ << ',' << dt_ << ',' << s.n_start << ',' << s.n_sourced << ',' << s.n_absorbed << ','
           << s.n_escaped << ',' << s.n_end << ',' << s.n_sent << ',' << s.n_received << ',' << s.n_block_crossings << ','
           << s.n_segments << ',' << s.n_scatters << ',' << s.n_ddmc_segments << ',' << s.n_bface_resampled << ',' << s.n_iterations << ',' << s.e_start
@@ -266,6 +268,13 @@ class Mcblock {
       }
     }
     Dump(-1);
+    if (rank_ == 0 && !opt_.quiet && ncycle_ > 0) {
+      // where the device time of the run went (jb_step_timeline; the reference's Kokkos regions, jaybenne.cpp:87-145)
+      static const char *names[9] = {"", "fields", "source", "transport", "exchange", "stats", "squeeze", "tally", "update"};
+      printf("device ms by phase over %ld cycles (rank 0, exchange mode %d):", ncycle_, pkg_->ExchangeMode());
+      for (int q = 1; q < 9; ++q) printf(" %s=%.3f", names[q], phase_ms_[q]);
+      printf("\n");
+    }
   }
 
   // <problem_id>.out0.<NNNNN|final>/r<rank>.<field>.npy
@@ -327,6 +336,7 @@ class Mcblock {
   std::string problem_id_;
   Real rho0_ = 0, tt0_ = 0, tlim_ = 0, out_dt_ = 0, time_ = 0, dt_ = 0;
   long nlim_ = -1, ncycle_ = 0;
+  double phase_ms_[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};  // device time per JB_TL_* phase, summed over the run
   bool thermal_ic_ = false;
   std::vector<std::pair<std::string, int32_t>> out_fields_;
 };
