@@ -244,6 +244,17 @@ jb_status jb_swarm_exchange(jb_ctx *ctx);  /* MeshResetCommunication+MeshSend+Me
 jb_status jb_sample_ddmc_block_face(jb_ctx *ctx);                          /* sample_ddmc_bface.cpp:81 */
 jb_status jb_check_completion(jb_ctx *ctx, double t_end, int64_t *num_unfinished); /* transport.cpp:187 */
 jb_status jb_evaluate_radiation_energy(jb_ctx *ctx);                       /* jaybenne.cpp:514 */
+/* The same tally for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc). NO counterpart in the reference. The call and everything
+ * below it allocates nothing: k_tally's scratch (per-cell accumulation buffer, census-energy bins, counters) is one
+ * file-scope device array of JB_NOALLOC_MAX_CELLS doubles + 8.3 KiB (2 MiB, held by every GPU that loads the library
+ * until exit). tally_out: tally_len >= local cells doubles, device or host memory, [local block][k][j][i];
+ * n_census / e_census (host, may be NULL): photons in the pool and the energy they carry. The context's own
+ * energy_tally field is not touched. More than JB_NOALLOC_MAX_CELLS local cells -> JB_ERR_CAPACITY. All calls share
+ * the array: calls that overlap on the GPU (two streams or contexts on one device) race. */
+#define JB_NOALLOC_MAX_CELLS 262144
+jb_status jb_evaluate_radiation_energy_noalloc(jb_ctx *ctx, double *tally_out, int64_t tally_len, int64_t *n_census,
+                                               double *e_census);
 jb_status jb_update_fluid(jb_ctx *ctx);                                    /* jaybenne.cpp:583 */
 /* mcblock's FillDerived after the step: sie = u / rho (mcblock.cpp:208-232) */
 jb_status jb_update_derived_material(jb_ctx *ctx);

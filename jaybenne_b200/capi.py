@@ -165,6 +165,7 @@ DEVICE_API = {
     "exchange_clear": (C.c_int, [ctx_p]),
     "set_sort_interval": (C.c_int, [ctx_p, C.c_int32]),
     "exchange_mode": (C.c_int32, [ctx_p]),
+    "evaluate_radiation_energy_noalloc": (C.c_int, [ctx_p, C.c_void_p, C.c_int64, C.POINTER(C.c_int64), _pd]),
     "step_timeline": (C.c_int, [ctx_p, C.POINTER(C.c_int32), C.POINTER(C.c_float), C.c_int32, C.POINTER(C.c_int32)]),
     "set_remote_field": (C.c_int, [ctx_p, C.c_int32, C.c_int32, C.c_void_p]),
     "set_fields": (C.c_int, [ctx_p, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_void_p)]),

@@ -1173,6 +1173,56 @@ void launch_tally(const StepParams &P, long long n, unsigned long long *n_alive,
   launch_fold_bins(P, EB_CENSUS, e_sum, st);
 }
 
+// ---------------------------------------------------------------------------------------
+// EvaluateRadiationEnergy without any allocation (jb_evaluate_radiation_energy_noalloc; no counterpart in the
+// reference, added for callers that cannot call cudaMalloc: CUDA graph
+// capture, tight serving loops, harnesses that forbid it). k_tally's scratch — the per-cell accumulation buffer,
+// the 1024 census-energy bins, the folded energy and the photon counter — lives in ONE file-scope device array of
+// a fixed, modest size (2 MiB + 8.3 KiB; every GPU that loads the library holds it until exit). In host code the
+// array's name is only a stand-in: its device address is looked up once per device with cudaGetSymbolAddress.
+// Every call shares the array (it keeps the last call's contents: what must start at zero is cleared here), so
+// calls that overlap on the GPU — two streams, two contexts on one device — race.
+// ---------------------------------------------------------------------------------------
+static constexpr long long NOALLOC_MAX_CELLS = 262144;  // 64^3 cells per rank
+static constexpr long long NOALLOC_DOUBLES = NOALLOC_MAX_CELLS + EBINS + 2;  // tally | bins | e_sum, n_alive (as u64)
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_DOUBLES];
+
+long long tally_noalloc_max_cells() { return NOALLOC_MAX_CELLS; }
+// tally_dst: ncells doubles (device or host), n_dst / e_dst: host. Returns the first CUDA error.
+cudaError_t launch_tally_noalloc(const StepParams &P0, long long n, double *tally_dst, long long *n_dst, double *e_dst,
+                                 cudaStream_t st) {
+  static double *scratch_of[64] = {nullptr};  // device address of the array, per device
+  int dev = 0;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) return err;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  if (!scratch_of[dev]) {
+    double *ptr = nullptr;
+    err = cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch);  // with `dev` current
+    if (err != cudaSuccess) return err;
+    scratch_of[dev] = ptr;
+  }
+  double *scr = scratch_of[dev];
+  const long long ncells = (long long)P0.mesh.nlocal * P0.mesh.ncell;
+  if (ncells > NOALLOC_MAX_CELLS) return cudaErrorInvalidValue;
+  StepParams P = P0;  // the same kernel, its scratch and outputs redirected into the static array
+  P.f.tally = scr;
+  // only the census bins are used by k_tally (kind EB_CENSUS): place the bin table so that kind's row is scr + ncells_max
+  P.ebins = scr + NOALLOC_MAX_CELLS - (long long)EB_CENSUS * EBINS;
+  double *e_sum = scr + NOALLOC_MAX_CELLS + EBINS;
+  unsigned long long *n_alive = reinterpret_cast<unsigned long long *>(scr + NOALLOC_MAX_CELLS + EBINS + 1);
+  err = cudaMemsetAsync(scr + NOALLOC_MAX_CELLS + EBINS, 0, 2 * sizeof(double), st);
+  if (err != cudaSuccess) return err;
+  launch_tally(P, n, n_alive, e_sum, st);  // clears the tally cells and the bins it uses, then k_tally + k_fold_bins
+  if ((err = cudaGetLastError()) != cudaSuccess) return err;
+  if (tally_dst && ncells > 0 &&
+      (err = cudaMemcpyAsync(tally_dst, scr, sizeof(double) * ncells, cudaMemcpyDefault, st)) != cudaSuccess)
+    return err;
+  if (e_dst && (err = cudaMemcpyAsync(e_dst, e_sum, sizeof(double), cudaMemcpyDeviceToHost, st)) != cudaSuccess) return err;
+  if (n_dst && (err = cudaMemcpyAsync(n_dst, n_alive, sizeof(long long), cudaMemcpyDeviceToHost, st)) != cudaSuccess) return err;
+  return cudaStreamSynchronize(st);
+}
+
 // UpdateFluid (jaybenne.cpp:603-612): u += energy_delta / dV
 __global__ void k_update_fluid(StepParams P, long long ncells) {
   const DMesh &m = P.mesh;

@@ -186,6 +186,9 @@ void launch_pack_props(const StepParams &P, cudaStream_t st);
 // folds ebins[kind] into *dst (dst = &stats->e_* or the census scratch)
 void launch_fold_bins(const StepParams &P, int kind, double *dst, cudaStream_t st);
 void launch_tally(const StepParams &P, long long n, unsigned long long *n_alive, double *e_sum, cudaStream_t st);
+long long tally_noalloc_max_cells();
+cudaError_t launch_tally_noalloc(const StepParams &P, long long n, double *tally_dst, long long *n_dst, double *e_dst,
+                                 cudaStream_t st);
 void launch_tally_sourced(const StepParams &P, unsigned long long *n_alive, double *e_sum, cudaStream_t st);
 void launch_update_fluid(const StepParams &P, cudaStream_t st);
 void launch_update_derived_material(const StepParams &P, cudaStream_t st);

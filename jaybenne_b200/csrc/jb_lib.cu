@@ -1157,6 +1157,30 @@ jb_status jb_evaluate_radiation_energy(jb_ctx *c) {
   return evaluate_radiation_energy(c, false);
 }
 
+// EvaluateRadiationEnergy for callers that may not allocate: no cudaMalloc / cudaFree in this call or below it
+// (launch_tally_noalloc: scratch in a file-scope device array). The context's own energy_tally field and census
+// cache are left untouched; the result goes to the caller's buffers.
+jb_status jb_evaluate_radiation_energy_noalloc(jb_ctx *c, double *tally_out, int64_t tally_len, int64_t *n_census,
+                                               double *e_census) {
+  JB_REQUIRE_MESH(c);
+  if (!tally_out) return fail(c, JB_ERR_INVALID, "jb_evaluate_radiation_energy_noalloc: tally_out is null");
+  if (c->ncells_local > tally_noalloc_max_cells())
+    return fail(c, JB_ERR_CAPACITY, "jb_evaluate_radiation_energy_noalloc: " + std::to_string(c->ncells_local) +
+                                        " local cells exceed the fixed scratch of " +
+                                        std::to_string(tally_noalloc_max_cells()) + " cells (JB_NOALLOC_MAX_CELLS)");
+  if (tally_len < c->ncells_local)
+    return fail(c, JB_ERR_INVALID, "jb_evaluate_radiation_energy_noalloc: tally_out holds fewer than the " +
+                                       std::to_string(c->ncells_local) + " local cells");
+  StepParams P = make_params(c);
+  long long n = 0;
+  double e = 0.0;
+  JB_CUDA(c, launch_tally_noalloc(P, c->n, tally_out, &n, &e, c->stream));
+  c->launches += 1 + (c->n > 0);
+  if (n_census) *n_census = (int64_t)n;
+  if (e_census) *e_census = e;
+  return JB_OK;
+}
+
 // InitializeRadiation on every local block (jaybenne.cpp:570-578). The reference sources
 // each block through its own MeshBlockData pack (nblocks = 1 in the per-cell count); the
 // blocks are independent, so one launch covers them all.

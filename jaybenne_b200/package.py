@@ -277,6 +277,16 @@ class Jaybenne:
         self._check(self.api.step_timeline(self._ctx, labels, ms, cap, C.byref(n)))
         return [(self.TL_NAMES.get(labels[q], str(labels[q])), float(ms[q])) for q in range(min(n.value, cap))]
 
+    def evaluate_radiation_energy_noalloc(self, out=None):
+        """(tally [local cells], photons in the pool, their energy) through jb_evaluate_radiation_energy_noalloc:
+        nothing is allocated on the device; `out` (float64, >= local cells) is the caller's result buffer."""
+        ncell = int(np.prod(self.nxb)) * len(self.local_gids)
+        a = out if out is not None else np.empty(ncell, dtype=np.float64)
+        n, e = C.c_int64(0), C.c_double(0.0)
+        self._check(self.api.evaluate_radiation_energy_noalloc(self._ctx, a.ctypes.data_as(C.c_void_p), a.size,
+                                                               C.byref(n), C.byref(e)))
+        return a[:ncell], n.value, e.value
+
     def set_sort_interval(self, every_n_cycles: int):
         self._check(self.api.set_sort_interval(self._ctx, int(every_n_cycles)))
 
