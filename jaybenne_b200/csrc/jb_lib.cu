@@ -339,6 +339,17 @@ static jb_status ensure_capacity(jb_ctx *c, long long need) {
   }
   JB_CUDA(c, dalloc(&c->out.count, std::max(c->n_ranks, 1)));
   JB_CUDA(c, cudaMemset(c->out.count, 0, sizeof(unsigned long long) * std::max(c->n_ranks, 1)));
+  // A pool the caller sized once (jb_set_capacity) also gets the scratch array of the order-preserving squeeze
+  // now: an 8 GB cudaMalloc in the middle of the first cycle that squeezes took 25-120 ms depending on the box
+  // (profiles/r02_v13_bench_default_cells256.json, variants.continuing, cycle 2). Failure is not an error here:
+  // compact() tries again and falls back to the in-place squeeze.
+  if (c->requested_capacity > 0 && !c->d_tmp) {
+    const char *v = getenv("JB_SQUEEZE");
+    if (!(v && strcmp(v, "tail") == 0) && dalloc(&c->d_tmp, c->capacity) != cudaSuccess) {
+      cudaGetLastError();
+      c->d_tmp = nullptr;
+    }
+  }
   return JB_OK;
 }
 
