@@ -626,10 +626,13 @@ static void launch_transport_hpool_b(const StepParams &P, long long first, long 
   static bool carved = false;
   if (!carved) {
     carved = true;
-    cudaFuncSetAttribute(k_transport_hpool<NDIM, MINB, S, ABS_GENERIC>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                         cudaSharedmemCarveoutMaxShared);
-    cudaFuncSetAttribute(k_transport_hpool<NDIM, MINB, S, ABS_GRAY_KIRCHHOFF>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                         cudaSharedmemCarveoutMaxShared);
+    // the shared-memory carve-out the pools need and no more: the rest of the SM's 256 KB is L1 for the per-cell
+    // records and face probabilities (as in k_transport_pool)
+    const long long per_cta = (long long)sizeof(HPool<S>) * POOL_WARPS + 32 + 1024;  // + the driver's 1 KB per CTA
+    int pct = (int)((per_cta * MINB * 100 + 233471) / 233472);
+    if (pct > 100) pct = 100;
+    cudaFuncSetAttribute(k_transport_hpool<NDIM, MINB, S, ABS_GENERIC>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+    cudaFuncSetAttribute(k_transport_hpool<NDIM, MINB, S, ABS_GRAY_KIRCHHOFF>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   }
   if (P.cl.opacity_model == JB_OPAC_GRAY && P.cl.gray_mode != JB_GRAY_DIRECT)
     k_transport_hpool<NDIM, MINB, S, ABS_GRAY_KIRCHHOFF><<<(unsigned)blocks, POOL_TPB, 0, st>>>(
